@@ -1,0 +1,170 @@
+// Microbenchmark: FP32-pipe, packed f32x2 and MUFU.RSQ issue rates on sm_100a.
+// Answers the design question in DESIGN.md ("scalar FFMA vs FFMA2 inner loop").
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -o fp32_pipes fp32_pipes.cu
+#include <cstdio>
+#include <cstdlib>
+#include <cuda_runtime.h>
+
+#define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { \
+    fprintf(stderr, "CUDA error %s at %s:%d\n", cudaGetErrorString(e_), __FILE__, __LINE__); exit(1); } } while (0)
+
+constexpr int ITERS = 4096;
+
+template <int ILP>
+__global__ void __launch_bounds__(256) k_ffma(float* out, float b, float c) {
+    float a[ILP];
+#pragma unroll
+    for (int k = 0; k < ILP; ++k) a[k] = threadIdx.x * 1e-3f + k;
+    for (int it = 0; it < ITERS; ++it) {
+#pragma unroll
+        for (int k = 0; k < ILP; ++k) a[k] = fmaf(a[k], b, c);
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < ILP; ++k) s += a[k];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
+// 3 distinct, varying register operands per FFMA (a = a*x + y with x,y per-k registers)
+template <int ILP>
+__global__ void __launch_bounds__(256) k_ffma3(float* out, float b, float c) {
+    float a[ILP], x[ILP], y[ILP];
+#pragma unroll
+    for (int k = 0; k < ILP; ++k) { a[k] = threadIdx.x * 1e-3f + k; x[k] = b + k * 1e-7f; y[k] = c + k; }
+    for (int it = 0; it < ITERS; ++it) {
+#pragma unroll
+        for (int k = 0; k < ILP; ++k) a[k] = fmaf(a[k], x[k], y[(k + 1) % ILP]);
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < ILP; ++k) s += a[k] + x[k] + y[k];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
+template <int ILP>
+__global__ void __launch_bounds__(256) k_ffma2(float* out, float b, float c) {
+    float2 a[ILP];
+    float2 bb = make_float2(b, b * 1.0001f), cc = make_float2(c, c * 0.999f);
+#pragma unroll
+    for (int k = 0; k < ILP; ++k) a[k] = make_float2(threadIdx.x * 1e-3f + k, k * 0.5f);
+    for (int it = 0; it < ITERS; ++it) {
+#pragma unroll
+        for (int k = 0; k < ILP; ++k) a[k] = __ffma2_rn(a[k], bb, cc);
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < ILP; ++k) s += a[k].x + a[k].y;
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
+template <int ILP>
+__global__ void __launch_bounds__(256) k_fadd2(float* out, float b, float c) {
+    float2 a[ILP];
+    float2 bb = make_float2(b, b * 1.0001f);
+#pragma unroll
+    for (int k = 0; k < ILP; ++k) a[k] = make_float2(threadIdx.x * 1e-3f + k, k * 0.5f);
+    for (int it = 0; it < ITERS; ++it) {
+#pragma unroll
+        for (int k = 0; k < ILP; ++k) a[k] = __fadd2_rn(a[k], bb);
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < ILP; ++k) s += a[k].x + a[k].y;
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
+template <int ILP>
+__global__ void __launch_bounds__(256) k_rsq(float* out, float b, float c) {
+    float a[ILP];
+#pragma unroll
+    for (int k = 0; k < ILP; ++k) a[k] = threadIdx.x * 1e-3f + k + 1.0f;
+    for (int it = 0; it < ITERS; ++it) {
+#pragma unroll
+        for (int k = 0; k < ILP; ++k) a[k] = rsqrtf(a[k]);   // MUFU.RSQ (+ denormal fix-up unless ftz)
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < ILP; ++k) s += a[k];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
+// MUFU.RSQ + NF dependent FFMAs per rsq, to see whether MUFU issue co-schedules with the FMA pipe.
+template <int ILP, int NF>
+__global__ void __launch_bounds__(256) k_mix(float* out, float b, float c) {
+    float a[ILP];
+#pragma unroll
+    for (int k = 0; k < ILP; ++k) a[k] = threadIdx.x * 1e-3f + k + 1.0f;
+    for (int it = 0; it < ITERS; ++it) {
+#pragma unroll
+        for (int k = 0; k < ILP; ++k) {
+            float r;
+            asm volatile("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(a[k]));
+#pragma unroll
+            for (int f = 0; f < NF; ++f) r = fmaf(r, b, c);
+            a[k] = r;
+        }
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < ILP; ++k) s += a[k];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
+// FSETP+FSEL (select) per FFMA: is compare/select on a different pipe from FFMA?
+template <int ILP>
+__global__ void __launch_bounds__(256) k_ffma_sel(float* out, float b, float c) {
+    float a[ILP];
+#pragma unroll
+    for (int k = 0; k < ILP; ++k) a[k] = threadIdx.x * 1e-3f + k;
+    for (int it = 0; it < ITERS; ++it) {
+#pragma unroll
+        for (int k = 0; k < ILP; ++k) { float t = fmaf(a[k], b, c); a[k] = (t >= c) ? t : 0.0f; }
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < ILP; ++k) s += a[k];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
+template <typename K>
+static void run(const char* name, K kern, int blocks_per_sm, double ops_per_thread_iter, int sms, float* d_out) {
+    int grid = sms * blocks_per_sm;
+    cudaEvent_t e0, e1;
+    CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    for (int w = 0; w < 3; ++w) kern<<<grid, 256>>>(d_out, 0.9999f, 1e-3f);
+    CK(cudaDeviceSynchronize());
+    float best = 1e30f;
+    for (int r = 0; r < 5; ++r) {
+        CK(cudaEventRecord(e0));
+        kern<<<grid, 256>>>(d_out, 0.9999f, 1e-3f);
+        CK(cudaEventRecord(e1));
+        CK(cudaEventSynchronize(e1));
+        float ms; CK(cudaEventElapsedTime(&ms, e0, e1));
+        if (ms < best) best = ms;
+    }
+    double ops = (double)grid * 256 * ITERS * ops_per_thread_iter;  // lane-ops
+    double per_s = ops / (best * 1e-3);
+    // lane-ops per clock per SM at the nominal 1965 MHz
+    printf("%-28s blocks/SM=%d  %.3f ms  %.3e lane-ops/s  %.1f lane-ops/clk/SM@1965MHz\n",
+           name, blocks_per_sm, best, per_s, per_s / sms / 1.965e9);
+}
+
+int main() {
+    cudaDeviceProp p; CK(cudaGetDeviceProperties(&p, 0));
+    int sms = p.multiProcessorCount;
+    printf("device %s, %d SMs, clockRate %d kHz\n", p.name, sms, p.clockRate);
+    float* d_out; CK(cudaMalloc(&d_out, (size_t)sms * 8 * 256 * sizeof(float)));
+    for (int bps : {4, 8}) {
+        run("ffma  (reg,const,const) ILP8", k_ffma<8>, bps, 8, sms, d_out);
+        run("ffma3 (3 distinct regs) ILP8", k_ffma3<8>, bps, 8, sms, d_out);
+        run("ffma2 packed ILP8 (x2 lanes)", k_ffma2<8>, bps, 16, sms, d_out);
+        run("ffma2 packed ILP4 (x2 lanes)", k_ffma2<4>, bps, 8, sms, d_out);
+        run("fadd2 packed ILP8 (x2 lanes)", k_fadd2<8>, bps, 16, sms, d_out);
+        run("rsqrtf ILP8", k_rsq<8>, bps, 8, sms, d_out);
+        run("mix rsq + 6 ffma ILP8", k_mix<8, 6>, bps, 8 * 7, sms, d_out);
+        run("mix rsq + 12 ffma ILP8", k_mix<8, 12>, bps, 8 * 13, sms, d_out);
+        run("ffma + setp/sel ILP8 (ffma only)", k_ffma_sel<8>, bps, 8, sms, d_out);
+    }
+    CK(cudaFree(d_out));
+    return 0;
+}
