@@ -1,0 +1,558 @@
+// gs_api.cu -- the C-ABI of libgravsim.so (include/gravsim.h): context, streams, step scheduling,
+// multi-GPU exchange.  Every entry point returns an error code; nothing throws across the boundary.
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+
+#include "../../include/gravsim.h"
+#include "gs_kernels.h"
+#include "gs_nccl_dyn.h"
+
+using namespace gs;
+
+struct gs_ctx {
+    gs_config cfg;
+    int device = 0;
+    int n = 0, n_pad = 0, slice = 0, i_begin = 0;   // slice = padded bodies per rank
+    int variant = 0, R = 0, i_tile = 0, cut_mode = 0;
+    int sm_count = 0, ctas_per_sm = 0, grid = 0, regs = 0;
+    float eps2 = 0.f, cut2 = 0.f;
+    float4* pos[2] = {nullptr, nullptr};
+    int cur = 0;
+    float4* vel = nullptr;        // this rank's slice
+    float4* vel_full = nullptr;   // world_size > 1: gathered velocities for download (lazy)
+    float4* acc_local = nullptr;  // world_size > 1: accelerations from the local j-slice
+    float4* acc_out = nullptr;    // gs_accel output (lazy)
+    float4* partial = nullptr;    // split-tile scratch
+    size_t partial_bytes = 0;
+    double* mass = nullptr;
+    void* d_aos = nullptr;        // staging for the reference-layout records
+    size_t d_aos_bytes = 0;
+    double* d_energy = nullptr;   // per-CTA partials: [egrid] potential + [egrid*4] kinetic/momentum + 8
+    double* h_energy = nullptr;   // pinned mirror
+    float4* h_acc = nullptr;      // pinned staging for gs_accel
+    size_t h_acc_bytes = 0;
+    cudaStream_t stream = nullptr, comm_stream = nullptr;
+    bool own_stream = false;
+    cudaEvent_t ev_integ = nullptr, ev_gather[2] = {nullptr, nullptr};
+    ncclComm_t comm = nullptr;
+    bool uploaded = false;
+    bool vel_synced = true;       // leapfrog: velocities at the same time as positions
+    uint64_t launches = 0;
+    int last_cuda_error = 0;
+    int64_t steps_done = 0;
+    bool split_full = false, split_local = false, split_remote = false;   // does a pass need the fix-up kernel
+};
+
+namespace {
+
+#define GS_CUDA(ctx, call)                                  \
+    do {                                                    \
+        cudaError_t e__ = (call);                           \
+        if (e__ != cudaSuccess) {                           \
+            (ctx)->last_cuda_error = (int)e__;              \
+            return GS_ECUDA;                                \
+        }                                                   \
+    } while (0)
+
+
+bool any_split(int64_t ni, int64_t nj, int grid) {
+    for (int64_t it = 0; it < ni; ++it)
+        if (tile_owners(ni, nj, grid, it).split) return true;
+    return false;
+}
+
+int ensure_aos(gs_ctx* c, size_t bytes) {
+    if (c->d_aos_bytes >= bytes) return GS_OK;
+    if (c->d_aos) cudaFree(c->d_aos);
+    c->d_aos = nullptr; c->d_aos_bytes = 0;
+    GS_CUDA(c, cudaMalloc(&c->d_aos, bytes));
+    c->d_aos_bytes = bytes;
+    return GS_OK;
+}
+
+// One force pass over this rank's i-bodies on the snapshot pos[cur].
+// world_size > 1 and overlap enabled: local j-slice first (needs nothing from the network), then
+// the remote slices once the all-gather of pos[cur] has landed.
+int force_pass(gs_ctx* c, int final_mode, float kick, float drift, float4* acc_out) {
+    StepParams p;
+    memset(&p, 0, sizeof(p));
+    p.pos_old = c->pos[c->cur];
+    p.pos_new = c->pos[c->cur ^ 1];
+    p.vel = c->vel;
+    p.partial = c->partial;
+    p.i_begin = c->i_begin;
+    p.n = c->n;
+    p.ni_tiles = c->slice / c->i_tile;
+    p.nj_total = c->n_pad / kJTile;
+    p.eps2 = c->eps2;
+    p.cut2 = c->cut2;
+    p.kick_dt = kick;
+    p.drift_dt = drift;
+    const int W = c->cfg.world_size;
+    // two passes: multi-GPU overlap, or GS_FLAG_TWO_PASS (same code path on one GPU, for tests)
+    const bool two_pass = ((W > 1) && !(c->cfg.flags & GS_FLAG_NO_OVERLAP)) ||
+                          ((W == 1) && (c->cfg.flags & GS_FLAG_TWO_PASS) && p.nj_total >= 2);
+    if (!two_pass) {
+        if (W > 1) GS_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_gather[c->cur], 0));
+        p.nj_tiles = p.nj_total; p.j_rot = 0;
+        p.acc_in = nullptr; p.acc_out = acc_out; p.final_mode = final_mode;
+        GS_CUDA(c, launch_force(c->variant, c->cut_mode, p, c->grid, c->stream)); c->launches++;
+        if (c->split_full) {
+            GS_CUDA(c, launch_fixup(c->variant, p, c->grid, c->stream)); c->launches++;
+        }
+        return GS_OK;
+    }
+    const int nj_local = (W > 1) ? c->slice / kJTile : p.nj_total / 2;
+    const int rot_local = (W > 1) ? c->cfg.rank * nj_local : p.nj_total / 4;
+    // pass L: j-tiles of this rank's own slice
+    p.nj_tiles = nj_local; p.j_rot = rot_local;
+    p.acc_in = nullptr; p.acc_out = c->acc_local; p.final_mode = kFinalAccOut;
+    GS_CUDA(c, launch_force(c->variant, c->cut_mode, p, c->grid, c->stream)); c->launches++;
+    if (c->split_local) {
+        GS_CUDA(c, launch_fixup(c->variant, p, c->grid, c->stream)); c->launches++;
+    }
+    // pass R: everything else, after the exchange
+    if (W > 1) GS_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_gather[c->cur], 0));
+    p.nj_tiles = p.nj_total - nj_local; p.j_rot = (rot_local + nj_local) % p.nj_total;
+    p.acc_in = c->acc_local; p.acc_out = acc_out; p.final_mode = final_mode;
+    GS_CUDA(c, launch_force(c->variant, c->cut_mode, p, c->grid, c->stream)); c->launches++;
+    if (c->split_remote) {
+        GS_CUDA(c, launch_fixup(c->variant, p, c->grid, c->stream)); c->launches++;
+    }
+    return GS_OK;
+}
+
+// Position exchange after an integrating pass wrote this rank's slice of pos[nxt]
+// (replaces MPI_Allgatherv + MPI_Barrier, mpi.c:227-236; 16 B/body instead of 56).
+int exchange_positions(gs_ctx* c, int nxt) {
+    if (c->cfg.world_size <= 1) return GS_OK;
+    NcclApi& nc = nccl_api();
+    GS_CUDA(c, cudaEventRecord(c->ev_integ, c->stream));
+    GS_CUDA(c, cudaStreamWaitEvent(c->comm_stream, c->ev_integ, 0));
+    const float4* send = c->pos[nxt] + c->i_begin;
+    ncclResult_t r = nc.AllGather(send, c->pos[nxt], (size_t)c->slice * 4, ncclFloat, c->comm, c->comm_stream);
+    if (r != ncclSuccess) return GS_ENCCL;
+    GS_CUDA(c, cudaEventRecord(c->ev_gather[nxt], c->comm_stream));
+    return GS_OK;
+}
+
+// Leapfrog keeps velocities half a step behind/ahead of the positions between steps; bring them
+// to the positions' time with a half kick from the current accelerations.
+int sync_velocities(gs_ctx* c) {
+    if (c->cfg.integrator != GS_INTEGRATOR_LEAPFROG || c->vel_synced) return GS_OK;
+    int rc = force_pass(c, kFinalKickOnly, (float)(0.5 * c->cfg.dt), 0.f, nullptr);
+    if (rc != GS_OK) return rc;
+    c->vel_synced = true;
+    return GS_OK;
+}
+
+int set_device(gs_ctx* c) {
+    GS_CUDA(c, cudaSetDevice(c->device));
+    return GS_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* gs_version(void) { return "gravsim-b200 0.1 (sm_100a)"; }
+
+const char* gs_strerror(int code) {
+    switch (code) {
+        case GS_OK: return "ok";
+        case GS_EINVAL: return "invalid argument";
+        case GS_ECUDA: return "CUDA runtime error (see gs_last_cuda_error)";
+        case GS_ENOMEM: return "out of memory";
+        case GS_ENCCL: return "NCCL unavailable or collective failed";
+        case GS_ESTATE: return "call out of order";
+        case GS_ENOGPU: return "no CUDA device available (libgravsim has no CPU path)";
+        case GS_EIO: return "state-file I/O error";
+        default: return "unknown error";
+    }
+}
+
+void gs_config_init(gs_config* cfg) {
+    if (!cfg) return;
+    memset(cfg, 0, sizeof(*cfg));
+    cfg->struct_size = (uint32_t)sizeof(gs_config);
+    cfg->dt = 3600.0;                 // cuda.cu:123, mpi.c:148
+    cfg->G = GS_G_SI;
+    cfg->eps = 0.0;
+    cfg->integrator = GS_INTEGRATOR_EULER;
+    cfg->device = -1;
+    cfg->rank = 0;
+    cfg->world_size = 1;
+}
+
+int gs_plan_tiles(int variant, int* i_tile, int* j_tile) {
+    if (variant == 0) variant = kDefaultVariant;
+    const int R = variant_bodies_per_thread(variant);
+    if (R == 0) return GS_EINVAL;
+    if (i_tile) *i_tile = kThreads * R;
+    if (j_tile) *j_tile = kJTile;
+    return GS_OK;
+}
+
+int gs_plan_slice(int n, int world_size, int rank, int variant, int* n_pad, int* i_begin_pad, int* i_end_pad) {
+    if (n <= 0 || world_size < 1 || rank < 0 || rank >= world_size) return GS_EINVAL;
+    if (variant == 0) variant = kDefaultVariant;
+    const int R = variant_bodies_per_thread(variant);
+    if (R == 0) return GS_EINVAL;
+    // every rank's slice is a whole number of i-tiles and of j-tiles
+    int64_t tile = (int64_t)kThreads * R;
+    int64_t unit = tile;
+    while (unit % kJTile != 0) unit += tile;
+    unit *= world_size;
+    const int64_t np = ((n + unit - 1) / unit) * unit;
+    if (np > INT32_MAX) return GS_EINVAL;
+    const int slice = (int)(np / world_size);
+    if (n_pad) *n_pad = (int)np;
+    if (i_begin_pad) *i_begin_pad = rank * slice;
+    if (i_end_pad) *i_end_pad = (rank + 1) * slice;
+    return GS_OK;
+}
+
+int gs_plan_cta_range(int64_t ni_tiles, int64_t nj_tiles, int grid, int cta, int64_t* u0, int64_t* u1) {
+    if (ni_tiles <= 0 || nj_tiles <= 0 || grid <= 0 || cta < 0 || cta >= grid) return GS_EINVAL;
+    const int64_t U = ni_tiles * nj_tiles;
+    if (u0) *u0 = cta_unit_begin(U, grid, cta);
+    if (u1) *u1 = cta_unit_begin(U, grid, cta + 1);
+    return GS_OK;
+}
+
+int gs_plan_tile_owners(int64_t ni_tiles, int64_t nj_tiles, int grid, int64_t it, int* cta_first, int* cta_last,
+                        int* is_split) {
+    if (ni_tiles <= 0 || nj_tiles <= 0 || grid <= 0 || it < 0 || it >= ni_tiles) return GS_EINVAL;
+    const TileOwners o = tile_owners(ni_tiles, nj_tiles, grid, it);
+    if (cta_first) *cta_first = o.first;
+    if (cta_last) *cta_last = o.last;
+    if (is_split) *is_split = o.split ? 1 : 0;
+    return GS_OK;
+}
+
+int gs_nccl_unique_id(void* out_id) {
+    if (!out_id) return GS_EINVAL;
+    NcclApi& nc = nccl_api();
+    if (!nc.ok) return GS_ENCCL;
+    ncclUniqueId id;
+    if (nc.GetUniqueId(&id) != ncclSuccess) return GS_ENCCL;
+    static_assert(sizeof(id) == GS_NCCL_ID_BYTES, "ncclUniqueId size");
+    memcpy(out_id, &id, sizeof(id));
+    return GS_OK;
+}
+
+int gs_host_alloc(void** ptr, size_t bytes) {
+    if (!ptr) return GS_EINVAL;
+    return cudaHostAlloc(ptr, bytes, cudaHostAllocDefault) == cudaSuccess ? GS_OK : GS_ENOMEM;
+}
+int gs_host_free(void* ptr) { return cudaFreeHost(ptr) == cudaSuccess ? GS_OK : GS_ECUDA; }
+
+void gs_destroy(gs_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    if (c->comm_stream) cudaStreamSynchronize(c->comm_stream);
+    if (c->comm) nccl_api().CommDestroy(c->comm);
+    cudaFree(c->pos[0]); cudaFree(c->pos[1]); cudaFree(c->vel); cudaFree(c->vel_full);
+    cudaFree(c->acc_local); cudaFree(c->acc_out); cudaFree(c->partial); cudaFree(c->mass);
+    cudaFree(c->d_aos); cudaFree(c->d_energy);
+    if (c->h_energy) cudaFreeHost(c->h_energy);
+    if (c->h_acc) cudaFreeHost(c->h_acc);
+    if (c->ev_integ) cudaEventDestroy(c->ev_integ);
+    for (int b = 0; b < 2; ++b)
+        if (c->ev_gather[b]) cudaEventDestroy(c->ev_gather[b]);
+    if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
+    if (c->comm_stream) cudaStreamDestroy(c->comm_stream);
+    delete c;
+}
+
+int gs_create(gs_ctx** out, const gs_config* cfg) {
+    if (!out || !cfg) return GS_EINVAL;
+    *out = nullptr;
+    if (cfg->struct_size != sizeof(gs_config)) return GS_EINVAL;
+    if (cfg->n <= 0 || cfg->world_size < 1 || cfg->rank < 0 || cfg->rank >= cfg->world_size) return GS_EINVAL;
+    if (!(cfg->G > 0.0) || !std::isfinite(cfg->dt) || !(cfg->eps >= 0.0)) return GS_EINVAL;
+    if (cfg->integrator != GS_INTEGRATOR_EULER && cfg->integrator != GS_INTEGRATOR_LEAPFROG) return GS_EINVAL;
+    if (cfg->world_size > 1 && !cfg->nccl_id) return GS_EINVAL;
+
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) return GS_ENOGPU;
+
+    gs_ctx* c = new (std::nothrow) gs_ctx();
+    if (!c) return GS_ENOMEM;
+    c->cfg = *cfg;
+    c->cfg.nccl_id = nullptr;
+    int rc = GS_OK;
+    auto fail = [&](int code) { gs_destroy(c); return code; };
+
+    if (cfg->device >= 0) c->device = cfg->device;
+    else if (cudaGetDevice(&c->device) != cudaSuccess) return fail(GS_ENOGPU);
+    if (c->device >= ndev) return fail(GS_EINVAL);
+    if ((rc = set_device(c)) != GS_OK) return fail(rc);
+
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, c->device) != cudaSuccess) return fail(GS_ECUDA);
+    if (prop.major < 10) return fail(GS_ENOGPU);   // sm_100a code only
+    c->sm_count = prop.multiProcessorCount;
+
+    c->variant = cfg->variant;
+    if (c->variant == 0) {
+        const char* ev = getenv("GRAVSIM_VARIANT");
+        c->variant = ev ? atoi(ev) : kDefaultVariant;
+    }
+    c->R = variant_bodies_per_thread(c->variant);
+    if (c->R == 0) return fail(GS_EINVAL);
+    c->i_tile = kThreads * c->R;
+    c->cut_mode = (cfg->eps > 0.0) ? kSoftened : kCutoff;
+    c->eps2 = (float)(cfg->eps * cfg->eps);
+    c->cut2 = (c->cut_mode == kCutoff) ? 1e-20f : 0.f;   // (1e-10)^2: cuda.cu:39, mpi.c:64
+
+    c->n = cfg->n;
+    int ib = 0, ie = 0;
+    if (gs_plan_slice(c->n, cfg->world_size, cfg->rank, c->variant, &c->n_pad, &ib, &ie) != GS_OK) return fail(GS_EINVAL);
+    c->i_begin = ib;
+    c->slice = ie - ib;
+
+    cudaError_t e = force_kernel_occupancy(c->variant, c->cut_mode, &c->ctas_per_sm, &c->regs);
+    if (e != cudaSuccess || c->ctas_per_sm < 1) { c->last_cuda_error = (int)e; return fail(GS_ECUDA); }
+    c->grid = c->sm_count * c->ctas_per_sm;
+    const char* eg = getenv("GRAVSIM_GRID");
+    if (eg && atoi(eg) > 0 && atoi(eg) <= c->grid) c->grid = atoi(eg);
+
+    {
+        const int64_t ni = c->slice / c->i_tile, nj = c->n_pad / kJTile, njl = c->slice / kJTile;
+        c->split_full = any_split(ni, nj, c->grid);
+        if (cfg->world_size > 1) {
+            c->split_local = any_split(ni, njl, c->grid);
+            c->split_remote = any_split(ni, nj - njl, c->grid);
+        } else if ((cfg->flags & GS_FLAG_TWO_PASS) && nj >= 2) {
+            c->split_local = any_split(ni, nj / 2, c->grid);
+            c->split_remote = any_split(ni, nj - nj / 2, c->grid);
+        }
+    }
+
+    auto dmalloc = [&](void** p, size_t bytes) { return cudaMalloc(p, bytes) == cudaSuccess; };
+    const size_t pos_bytes = (size_t)c->n_pad * sizeof(float4);
+    const size_t vel_bytes = (size_t)c->slice * sizeof(float4);
+    c->partial_bytes = (size_t)c->grid * 2 * c->i_tile * sizeof(float4);
+    const int egrid = energy_grid(c->slice);
+    if (!dmalloc((void**)&c->pos[0], pos_bytes) || !dmalloc((void**)&c->pos[1], pos_bytes) ||
+        !dmalloc((void**)&c->vel, vel_bytes) || !dmalloc((void**)&c->partial, c->partial_bytes) ||
+        !dmalloc((void**)&c->mass, (size_t)c->n_pad * sizeof(double)) ||
+        !dmalloc((void**)&c->d_energy, ((size_t)egrid * 5 + 8) * sizeof(double)))
+        return fail(GS_ENOMEM);
+    if ((cfg->world_size > 1 || (cfg->flags & GS_FLAG_TWO_PASS)) && !dmalloc((void**)&c->acc_local, vel_bytes))
+        return fail(GS_ENOMEM);
+    if (cudaHostAlloc((void**)&c->h_energy, ((size_t)egrid * 5 + 8) * sizeof(double), cudaHostAllocDefault) !=
+        cudaSuccess)
+        return fail(GS_ENOMEM);
+
+    if (cfg->stream) { c->stream = (cudaStream_t)cfg->stream; c->own_stream = false; }
+    else {
+        if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) return fail(GS_ECUDA);
+        c->own_stream = true;
+    }
+    if (cudaEventCreateWithFlags(&c->ev_integ, cudaEventDisableTiming) != cudaSuccess) return fail(GS_ECUDA);
+    for (int b = 0; b < 2; ++b)
+        if (cudaEventCreateWithFlags(&c->ev_gather[b], cudaEventDisableTiming) != cudaSuccess) return fail(GS_ECUDA);
+
+    if (cfg->world_size > 1) {
+        NcclApi& nc = nccl_api();
+        if (!nc.ok) return fail(GS_ENCCL);
+        if (cudaStreamCreateWithFlags(&c->comm_stream, cudaStreamNonBlocking) != cudaSuccess) return fail(GS_ECUDA);
+        ncclUniqueId id;
+        memcpy(&id, cfg->nccl_id, sizeof(id));
+        if (nc.CommInitRank(&c->comm, cfg->world_size, id, cfg->rank) != ncclSuccess) return fail(GS_ENCCL);
+    }
+    *out = c;
+    return GS_OK;
+}
+
+static int upload_common(gs_ctx* c, const void* host, int n, int record_bytes) {
+    if (!c || !host) return GS_EINVAL;
+    if (n != c->n) return GS_EINVAL;
+    int rc = set_device(c);
+    if (rc != GS_OK) return rc;
+    const size_t bytes = (size_t)n * record_bytes;
+    if ((rc = ensure_aos(c, bytes)) != GS_OK) return rc;
+    GS_CUDA(c, cudaMemcpyAsync(c->d_aos, host, bytes, cudaMemcpyHostToDevice, c->stream));
+    c->cur = 0;
+    GS_CUDA(c, launch_aos_to_packed(c->d_aos, record_bytes, n, c->n_pad, c->cfg.G, c->pos[0], c->vel, c->mass,
+                                    c->i_begin, c->slice, c->stream));
+    c->launches++;
+    // the other buffer must carry mu and the padding too: remote slices are filled by the exchange,
+    // the own slice by the integrator, but the padding bodies of a single-GPU run are only ever
+    // written here.
+    GS_CUDA(c, cudaMemcpyAsync(c->pos[1], c->pos[0], (size_t)c->n_pad * sizeof(float4), cudaMemcpyDeviceToDevice,
+                               c->stream));
+    if (c->cfg.world_size > 1) {
+        // every rank uploaded the full array: pos[0] is already "gathered"
+        GS_CUDA(c, cudaEventRecord(c->ev_integ, c->stream));
+        GS_CUDA(c, cudaStreamWaitEvent(c->comm_stream, c->ev_integ, 0));
+        GS_CUDA(c, cudaEventRecord(c->ev_gather[0], c->comm_stream));
+    }
+    c->uploaded = true;
+    c->vel_synced = true;
+    c->steps_done = 0;
+    return GS_OK;
+}
+
+int gs_upload_aos_f32(gs_ctx* ctx, const void* particles28, int n) { return upload_common(ctx, particles28, n, 28); }
+int gs_upload_aos_f64(gs_ctx* ctx, const void* particles56, int n) { return upload_common(ctx, particles56, n, 56); }
+
+int gs_step(gs_ctx* c, int nsteps) {
+    if (!c || nsteps < 0) return GS_EINVAL;
+    if (!c->uploaded) return GS_ESTATE;
+    int rc = set_device(c);
+    if (rc != GS_OK) return rc;
+    const float dt = (float)c->cfg.dt;
+    for (int s = 0; s < nsteps; ++s) {
+        float kick = dt;
+        if (c->cfg.integrator == GS_INTEGRATOR_LEAPFROG && c->vel_synced) kick = 0.5f * dt;   // opening half kick
+        if ((rc = force_pass(c, kFinalIntegrate, kick, dt, nullptr)) != GS_OK) return rc;
+        const int nxt = c->cur ^ 1;
+        if ((rc = exchange_positions(c, nxt)) != GS_OK) return rc;
+        c->cur = nxt;
+        if (c->cfg.integrator == GS_INTEGRATOR_LEAPFROG) c->vel_synced = false;
+        c->steps_done++;
+    }
+    return GS_OK;
+}
+
+int gs_accel(gs_ctx* c, float* acc3_host) {
+    if (!c || !acc3_host) return GS_EINVAL;
+    if (!c->uploaded) return GS_ESTATE;
+    int rc = set_device(c);
+    if (rc != GS_OK) return rc;
+    const size_t bytes = (size_t)c->slice * sizeof(float4);
+    if (!c->acc_out) GS_CUDA(c, cudaMalloc((void**)&c->acc_out, bytes));
+    if (c->h_acc_bytes < bytes) {
+        if (c->h_acc) cudaFreeHost(c->h_acc);
+        c->h_acc = nullptr; c->h_acc_bytes = 0;
+        GS_CUDA(c, cudaHostAlloc((void**)&c->h_acc, bytes, cudaHostAllocDefault));
+        c->h_acc_bytes = bytes;
+    }
+    if ((rc = force_pass(c, kFinalAccOut, 0.f, 0.f, c->acc_out)) != GS_OK) return rc;
+    int n_local = c->n - c->i_begin;
+    if (n_local > c->slice) n_local = c->slice;
+    if (n_local < 0) n_local = 0;
+    GS_CUDA(c, cudaMemcpyAsync(c->h_acc, c->acc_out, (size_t)n_local * sizeof(float4), cudaMemcpyDeviceToHost,
+                               c->stream));
+    GS_CUDA(c, cudaStreamSynchronize(c->stream));
+    for (int i = 0; i < n_local; ++i) {
+        acc3_host[3 * (size_t)i + 0] = c->h_acc[i].x;
+        acc3_host[3 * (size_t)i + 1] = c->h_acc[i].y;
+        acc3_host[3 * (size_t)i + 2] = c->h_acc[i].z;
+    }
+    return GS_OK;
+}
+
+int gs_energy(gs_ctx* c, double* kinetic, double* potential, double momentum[3]) {
+    if (!c) return GS_EINVAL;
+    if (!c->uploaded) return GS_ESTATE;
+    int rc = set_device(c);
+    if (rc != GS_OK) return rc;
+    if ((rc = sync_velocities(c)) != GS_OK) return rc;
+    if (c->cfg.world_size > 1) GS_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_gather[c->cur], 0));
+    const int egrid = energy_grid(c->slice);
+    double* d_pot = c->d_energy;
+    double* d_kin = c->d_energy + egrid;
+    double* d_red = c->d_energy + (size_t)egrid * 5;
+    GS_CUDA(c, launch_potential(c->pos[c->cur], c->n_pad, c->i_begin, c->slice, c->eps2, c->cut2, d_pot, c->stream));
+    GS_CUDA(c, launch_kinetic(c->vel, c->mass, c->i_begin, c->slice, d_kin, c->stream));
+    c->launches += 2;
+    GS_CUDA(c, cudaMemcpyAsync(c->h_energy, c->d_energy, (size_t)egrid * 5 * sizeof(double), cudaMemcpyDeviceToHost,
+                               c->stream));
+    GS_CUDA(c, cudaStreamSynchronize(c->stream));
+    double v[5] = {0, 0, 0, 0, 0};   // {sum mu_i phi_i, sum m v^2, px, py, pz}
+    for (int b = 0; b < egrid; ++b) {
+        v[0] += c->h_energy[b];
+        for (int k = 0; k < 4; ++k) v[1 + k] += c->h_energy[egrid + 4 * b + k];
+    }
+    if (c->cfg.world_size > 1) {
+        NcclApi& nc = nccl_api();
+        double* h_red = c->h_energy + (size_t)egrid * 5;
+        memcpy(h_red, v, sizeof(v));
+        GS_CUDA(c, cudaMemcpyAsync(d_red, h_red, sizeof(v), cudaMemcpyHostToDevice, c->stream));
+        if (nc.AllReduce(d_red, d_red, 5, ncclDouble, ncclSum, c->comm, c->stream) != ncclSuccess) return GS_ENCCL;
+        GS_CUDA(c, cudaMemcpyAsync(h_red, d_red, sizeof(v), cudaMemcpyDeviceToHost, c->stream));
+        GS_CUDA(c, cudaStreamSynchronize(c->stream));
+        memcpy(v, h_red, sizeof(v));
+    }
+    // U = -sum_{i<j} G m_i m_j / d = -(1/(2G)) sum_i mu_i sum_{j!=i} mu_j / d
+    if (potential) *potential = -0.5 * v[0] / c->cfg.G;
+    if (kinetic) *kinetic = 0.5 * v[1];
+    if (momentum) { momentum[0] = v[2]; momentum[1] = v[3]; momentum[2] = v[4]; }
+    return GS_OK;
+}
+
+static int download_common(gs_ctx* c, void* host, int n, int record_bytes) {
+    if (!c || !host) return GS_EINVAL;
+    if (!c->uploaded) return GS_ESTATE;
+    if (n != c->n) return GS_EINVAL;
+    int rc = set_device(c);
+    if (rc != GS_OK) return rc;
+    if ((rc = sync_velocities(c)) != GS_OK) return rc;
+    const float4* vel_full = c->vel;
+    if (c->cfg.world_size > 1) {
+        NcclApi& nc = nccl_api();
+        if (!c->vel_full) GS_CUDA(c, cudaMalloc((void**)&c->vel_full, (size_t)c->n_pad * sizeof(float4)));
+        GS_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_gather[c->cur], 0));
+        if (nc.AllGather(c->vel, c->vel_full, (size_t)c->slice * 4, ncclFloat, c->comm, c->stream) != ncclSuccess)
+            return GS_ENCCL;
+        vel_full = c->vel_full;
+    }
+    const size_t bytes = (size_t)n * record_bytes;
+    if ((rc = ensure_aos(c, bytes)) != GS_OK) return rc;
+    GS_CUDA(c, launch_packed_to_aos(c->pos[c->cur], vel_full, c->mass, n, c->d_aos, record_bytes, c->stream));
+    c->launches++;
+    GS_CUDA(c, cudaMemcpyAsync(host, c->d_aos, bytes, cudaMemcpyDeviceToHost, c->stream));
+    GS_CUDA(c, cudaStreamSynchronize(c->stream));
+    return GS_OK;
+}
+
+int gs_download_aos_f32(gs_ctx* ctx, void* particles28, int n) { return download_common(ctx, particles28, n, 28); }
+int gs_download_aos_f64(gs_ctx* ctx, void* particles56, int n) { return download_common(ctx, particles56, n, 56); }
+
+int gs_sync(gs_ctx* c) {
+    if (!c) return GS_EINVAL;
+    int rc = set_device(c);
+    if (rc != GS_OK) return rc;
+    GS_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (c->comm_stream) GS_CUDA(c, cudaStreamSynchronize(c->comm_stream));
+    return GS_OK;
+}
+
+int gs_set_dt(gs_ctx* c, double dt) {
+    if (!c || !std::isfinite(dt)) return GS_EINVAL;
+    if (c->cfg.integrator == GS_INTEGRATOR_LEAPFROG && !c->vel_synced) {
+        int rc = set_device(c);
+        if (rc != GS_OK) return rc;
+        if ((rc = sync_velocities(c)) != GS_OK) return rc;   // close the step with the old dt first
+    }
+    c->cfg.dt = dt;
+    return GS_OK;
+}
+
+int gs_get_info(const gs_ctx* c, gs_info* info) {
+    if (!c || !info) return GS_EINVAL;
+    memset(info, 0, sizeof(*info));
+    info->n = c->n; info->n_pad = c->n_pad;
+    info->i_begin = c->i_begin < c->n ? c->i_begin : c->n;
+    const int ie = c->i_begin + c->slice;
+    info->i_end = ie < c->n ? ie : c->n;
+    info->sm_count = c->sm_count; info->grid = c->grid;
+    info->i_tile = c->i_tile; info->j_tile = kJTile;
+    info->stages = kStages; info->variant = c->variant;
+    info->regs_per_thread = c->regs; info->threads = kThreads;
+    info->scratch_bytes = (int64_t)c->partial_bytes;
+    return GS_OK;
+}
+
+uint64_t gs_kernel_launches(const gs_ctx* c) { return c ? c->launches : 0; }
+int gs_last_cuda_error(const gs_ctx* c) { return c ? c->last_cuda_error : 0; }
+
+}  // extern "C"

@@ -1,0 +1,559 @@
+// gs_kernels.cu -- hand-written sm_100a kernels of the direct all-pairs gravity engine.
+//
+// Replaces the reference's calculate_forces_kernel + calculate_force_between (cuda.cu:32-60),
+// its serial host update (cuda.cu:63-78) and mpi.c's force row + integrator (mpi.c:196-216).
+//
+// Force kernel (force_step_kernel):
+//   * persistent CTAs, one static "stream-K" slice of the (i-tile x j-tile) unit space each
+//     (gs_layout.h), so all 148 SMs finish together whatever N is;
+//   * j-tiles (512 bodies, 8 KB) streamed into a 4-stage shared-memory ring by TMA bulk copies
+//     (cp.async.bulk -> UBLKCP) that complete on mbarriers; one elected thread refills a stage two
+//     tiles after the CTA's warps released it (empty mbarrier), nobody waits on __syncthreads;
+//   * R i-bodies register-blocked per thread; every 128-bit broadcast LDS delivers one j-PAIR as
+//     (even,odd) register pairs, consumed by packed FADD2/FFMA2/FMUL2 (two interactions per
+//     instruction) and two MUFU.RSQ;
+//   * two-level fp32 accumulation: per-tile packed partials flushed into per-body outer sums
+//     (keeps the per-body relative error ~1e-6);
+//   * the Euler / leapfrog velocity+position update is fused into the epilogue of every i-tile
+//     that one CTA saw completely; the few split tiles leave partial sums in scratch and are
+//     finished by fixup_kernel.
+// There are no tensor-core instructions: the interaction is not a dense contraction.
+#include "gs_kernels.h"
+
+namespace gs {
+
+// ------------------------------------------------------------------------------------------------
+// PTX helpers: mbarrier + TMA bulk copy
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+    return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void fence_mbar_init() {
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "GS_WAIT:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra GS_DONE;\n"
+        "bra GS_WAIT;\n"
+        "GS_DONE:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+// 1-D TMA bulk copy global -> shared, completion signalled on an mbarrier (SASS: UBLKCP).
+__device__ __forceinline__ void tma_bulk_g2s(void* smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(smem_dst)),
+                 "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ float rsqrt_approx(float x) {
+    float r;
+    asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));   // MUFU.RSQ, nothing else
+    return r;
+}
+
+// ------------------------------------------------------------------------------------------------
+// finishing one i-pair: add upstream accelerations, then write them out or integrate
+//   v += a * kick_dt ; x += v_new * drift_dt          (cuda.cu:73-76, mpi.c:207-215)
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void finish_pair(const StepParams& p, int pair_local, float4 a0, float4 a1) {
+    if (p.acc_in != nullptr) {
+        const float4 b0 = p.acc_in[2 * pair_local], b1 = p.acc_in[2 * pair_local + 1];
+        a0.x += b0.x; a0.y += b0.y; a0.z += b0.z;
+        a1.x += b1.x; a1.y += b1.y; a1.z += b1.z;
+    }
+    const int body0 = p.i_begin + 2 * pair_local;   // padding bodies stay put (massless, at rest)
+    if (body0 >= p.n) a0 = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (body0 + 1 >= p.n) a1 = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (p.final_mode == kFinalAccOut) {
+        a0.w = 0.f; a1.w = 0.f;
+        p.acc_out[2 * pair_local] = a0;
+        p.acc_out[2 * pair_local + 1] = a1;
+        return;
+    }
+    const int pair_global = (p.i_begin >> 1) + pair_local;
+    float4 VA = p.vel[2 * pair_local], VB = p.vel[2 * pair_local + 1];
+    float4 PA = p.pos_old[2 * pair_global], PB = p.pos_old[2 * pair_global + 1];
+    VA.x = fmaf(a0.x, p.kick_dt, VA.x); VA.y = fmaf(a1.x, p.kick_dt, VA.y);
+    VA.z = fmaf(a0.y, p.kick_dt, VA.z); VA.w = fmaf(a1.y, p.kick_dt, VA.w);
+    VB.x = fmaf(a0.z, p.kick_dt, VB.x); VB.y = fmaf(a1.z, p.kick_dt, VB.y);
+    p.vel[2 * pair_local] = VA; p.vel[2 * pair_local + 1] = VB;
+    if (p.final_mode == kFinalKickOnly) return;
+    PA.x = fmaf(VA.x, p.drift_dt, PA.x); PA.y = fmaf(VA.y, p.drift_dt, PA.y);
+    PA.z = fmaf(VA.z, p.drift_dt, PA.z); PA.w = fmaf(VA.w, p.drift_dt, PA.w);
+    PB.x = fmaf(VB.x, p.drift_dt, PB.x); PB.y = fmaf(VB.y, p.drift_dt, PB.y);
+    p.pos_new[2 * pair_global] = PA; p.pos_new[2 * pair_global + 1] = PB;   // PB.zw = mu, unchanged
+}
+
+// ------------------------------------------------------------------------------------------------
+// the force kernel
+// ------------------------------------------------------------------------------------------------
+template <int R>
+struct Acc {
+    float x[R], y[R], z[R];
+};
+
+// One j-tile against this thread's R i-bodies, packed f32x2: per j-PAIR and i-body
+//   3 FADD2 + 3 FFMA2 + 2 MUFU.RSQ (+ 2 FSETP/FSEL in cutoff mode) + 3 FMUL2 + 3 FFMA2.
+template <int R, int CUT>
+__device__ __forceinline__ void tile_packed(const float4* __restrict__ T, const float2 (&nxi)[R],
+                                            const float2 (&nyi)[R], const float2 (&nzi)[R], float2 eps2,
+                                            float cut2, Acc<R>& out) {
+    float2 ax[R], ay[R], az[R];
+#pragma unroll
+    for (int b = 0; b < R; ++b) ax[b] = ay[b] = az[b] = make_float2(0.f, 0.f);
+#pragma unroll 2
+    for (int jp = 0; jp < kJTile / 2; ++jp) {
+        const float4 A = T[2 * jp], B = T[2 * jp + 1];
+        const float2 xj = make_float2(A.x, A.y), yj = make_float2(A.z, A.w);
+        const float2 zj = make_float2(B.x, B.y), mj = make_float2(B.z, B.w);
+#pragma unroll
+        for (int b = 0; b < R; ++b) {
+            const float2 dx = __fadd2_rn(xj, nxi[b]);
+            const float2 dy = __fadd2_rn(yj, nyi[b]);
+            const float2 dz = __fadd2_rn(zj, nzi[b]);
+            float2 r2 = __ffma2_rn(dx, dx, eps2);
+            r2 = __ffma2_rn(dy, dy, r2);
+            r2 = __ffma2_rn(dz, dz, r2);
+            float2 ri = make_float2(rsqrt_approx(r2.x), rsqrt_approx(r2.y));
+            if (CUT == kCutoff) {   // reference rule: r < 1e-10 contributes nothing (cuda.cu:39, mpi.c:64)
+                ri.x = (r2.x >= cut2) ? ri.x : 0.f;
+                ri.y = (r2.y >= cut2) ? ri.y : 0.f;
+            }
+            const float2 ri2 = __fmul2_rn(ri, ri);
+            float2 s = __fmul2_rn(mj, ri);      // (mu * rinv) * rinv^2: no overflow in SI units
+            s = __fmul2_rn(s, ri2);
+            ax[b] = __ffma2_rn(s, dx, ax[b]);
+            ay[b] = __ffma2_rn(s, dy, ay[b]);
+            az[b] = __ffma2_rn(s, dz, az[b]);
+        }
+    }
+#pragma unroll
+    for (int b = 0; b < R; ++b) {   // level-2 accumulation (flush the tile partials)
+        out.x[b] += ax[b].x + ax[b].y;
+        out.y[b] += ay[b].x + ay[b].y;
+        out.z[b] += az[b].x + az[b].y;
+    }
+}
+
+// Scalar FP32 variant of the same tile (12 FP32-pipe + 1 MUFU issue slots per interaction), kept
+// as the measured comparison for the packed path.
+template <int R, int CUT>
+__device__ __forceinline__ void tile_scalar(const float4* __restrict__ T, const float2 (&nxi)[R],
+                                            const float2 (&nyi)[R], const float2 (&nzi)[R], float2 eps2,
+                                            float cut2, Acc<R>& out) {
+    float ax[R], ay[R], az[R], bx[R], by[R], bz[R];
+#pragma unroll
+    for (int b = 0; b < R; ++b) ax[b] = ay[b] = az[b] = bx[b] = by[b] = bz[b] = 0.f;
+#pragma unroll 2
+    for (int jp = 0; jp < kJTile / 2; ++jp) {
+        const float4 A = T[2 * jp], B = T[2 * jp + 1];
+#pragma unroll
+        for (int b = 0; b < R; ++b) {
+            {
+                const float dx = A.x + nxi[b].x, dy = A.z + nyi[b].x, dz = B.x + nzi[b].x;
+                float r2 = fmaf(dx, dx, eps2.x); r2 = fmaf(dy, dy, r2); r2 = fmaf(dz, dz, r2);
+                float ri = rsqrt_approx(r2);
+                if (CUT == kCutoff) ri = (r2 >= cut2) ? ri : 0.f;
+                const float s = (B.z * ri) * (ri * ri);
+                ax[b] = fmaf(s, dx, ax[b]); ay[b] = fmaf(s, dy, ay[b]); az[b] = fmaf(s, dz, az[b]);
+            }
+            {
+                const float dx = A.y + nxi[b].x, dy = A.w + nyi[b].x, dz = B.y + nzi[b].x;
+                float r2 = fmaf(dx, dx, eps2.x); r2 = fmaf(dy, dy, r2); r2 = fmaf(dz, dz, r2);
+                float ri = rsqrt_approx(r2);
+                if (CUT == kCutoff) ri = (r2 >= cut2) ? ri : 0.f;
+                const float s = (B.w * ri) * (ri * ri);
+                bx[b] = fmaf(s, dx, bx[b]); by[b] = fmaf(s, dy, by[b]); bz[b] = fmaf(s, dz, bz[b]);
+            }
+        }
+    }
+#pragma unroll
+    for (int b = 0; b < R; ++b) {
+        out.x[b] += ax[b] + bx[b];
+        out.y[b] += ay[b] + by[b];
+        out.z[b] += az[b] + bz[b];
+    }
+}
+
+constexpr size_t kTileBytes = (size_t)kJTile * sizeof(float4);
+constexpr size_t kSmemBytes = kStages * kTileBytes + 2 * kStages * sizeof(uint64_t);
+
+template <int R, int CUT, bool PACKED>
+__global__ void __launch_bounds__(kThreads, (R <= 4) ? 2 : 1) force_step_kernel(const StepParams p) {
+    static_assert(R % 2 == 0, "threads own whole i-pairs");
+    constexpr int ITILE = kThreads * R;
+    constexpr int NP = R / 2;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    float4* tiles = reinterpret_cast<float4*>(smem_raw);
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + kStages * kTileBytes);
+    uint64_t* empty = full + kStages;
+
+    const int tid = threadIdx.x;
+    const int64_t U = (int64_t)p.ni_tiles * p.nj_tiles;
+    const int64_t u0 = cta_unit_begin(U, gridDim.x, blockIdx.x);
+    const int64_t u1 = cta_unit_begin(U, gridDim.x, blockIdx.x + 1);
+    const int nunits = (int)(u1 - u0);
+    if (nunits <= 0) return;
+    const int64_t first_tile = u0 / p.nj_tiles;
+
+    if (tid == 0) {
+#pragma unroll
+        for (int s = 0; s < kStages; ++s) {
+            mbar_init(&full[s], 1);
+            mbar_init(&empty[s], kThreads / 32);
+        }
+        fence_mbar_init();
+    }
+    __syncthreads();
+
+    // physical source of the k-th unit's j-tile
+    auto tile_src = [&](int k) -> const float4* {
+        int v = (int)((u0 + k) % p.nj_tiles);
+        int phys = v + p.j_rot;
+        if (phys >= p.nj_total) phys -= p.nj_total;
+        return p.pos_old + (size_t)phys * kJTile;
+    };
+    if (tid == 0) {
+        for (int k = 0; k < kStages && k < nunits; ++k) {
+            mbar_arrive_expect_tx(&full[k], (uint32_t)kTileBytes);
+            tma_bulk_g2s(tiles + (size_t)k * kJTile, tile_src(k), (uint32_t)kTileBytes, &full[k]);
+        }
+    }
+
+    const float2 eps2 = make_float2(p.eps2, p.eps2);
+    int k = 0;
+    while (k < nunits) {
+        const int64_t u = u0 + k;
+        const int64_t it = u / p.nj_tiles;
+        const int jv = (int)(u - it * p.nj_tiles);
+        const int seg = min(p.nj_tiles - jv, nunits - k);
+        const bool whole = (jv == 0) && (seg == p.nj_tiles);
+
+        // this thread's R i-bodies (NP pairs), negated and duplicated for the packed subtract
+        float2 nxi[R], nyi[R], nzi[R];
+        Acc<R> acc;
+#pragma unroll
+        for (int q = 0; q < NP; ++q) {
+            const int pair_local = (int)it * (ITILE / 2) + q * kThreads + tid;
+            const int pair_global = (p.i_begin >> 1) + pair_local;
+            const float4 A = p.pos_old[2 * pair_global], B = p.pos_old[2 * pair_global + 1];
+            nxi[2 * q] = make_float2(-A.x, -A.x); nxi[2 * q + 1] = make_float2(-A.y, -A.y);
+            nyi[2 * q] = make_float2(-A.z, -A.z); nyi[2 * q + 1] = make_float2(-A.w, -A.w);
+            nzi[2 * q] = make_float2(-B.x, -B.x); nzi[2 * q + 1] = make_float2(-B.y, -B.y);
+        }
+#pragma unroll
+        for (int b = 0; b < R; ++b) acc.x[b] = acc.y[b] = acc.z[b] = 0.f;
+
+        for (int t = 0; t < seg; ++t, ++k) {
+            const int stage = k % kStages;
+            if (tid == 0 && k >= kRefillLag) {   // refill the stage used kRefillLag tiles ago
+                const int kr = k - kRefillLag, kn = kr + kStages;
+                if (kn < nunits) {
+                    const int sr = kr % kStages;
+                    mbar_wait(&empty[sr], (uint32_t)((kr / kStages) & 1));
+                    mbar_arrive_expect_tx(&full[sr], (uint32_t)kTileBytes);
+                    tma_bulk_g2s(tiles + (size_t)sr * kJTile, tile_src(kn), (uint32_t)kTileBytes, &full[sr]);
+                }
+            }
+            mbar_wait(&full[stage], (uint32_t)((k / kStages) & 1));
+            const float4* T = tiles + (size_t)stage * kJTile;
+            if (PACKED) tile_packed<R, CUT>(T, nxi, nyi, nzi, eps2, p.cut2, acc);
+            else tile_scalar<R, CUT>(T, nxi, nyi, nzi, eps2, p.cut2, acc);
+            __syncwarp();
+            if ((tid & 31) == 0) mbar_arrive(&empty[stage]);
+        }
+
+        // epilogue of this (i-tile, j-range) segment
+#pragma unroll
+        for (int q = 0; q < NP; ++q) {
+            const int in_tile = 2 * (q * kThreads + tid);            // first body of the pair, in the tile
+            const float4 a0 = make_float4(acc.x[2 * q], acc.y[2 * q], acc.z[2 * q], 0.f);
+            const float4 a1 = make_float4(acc.x[2 * q + 1], acc.y[2 * q + 1], acc.z[2 * q + 1], 0.f);
+            if (whole) {
+                finish_pair(p, (int)it * (ITILE / 2) + q * kThreads + tid, a0, a1);
+            } else {
+                const int slot = (it == first_tile) ? 0 : 1;
+                float4* dst = p.partial + ((size_t)blockIdx.x * 2 + slot) * ITILE + in_tile;
+                dst[0] = a0; dst[1] = a1;
+            }
+        }
+    }
+}
+
+template <int R>
+__global__ void __launch_bounds__(256) fixup_kernel(const StepParams p, int grid_main) {
+    constexpr int ITILE = kThreads * R;
+    const int pair_local = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pair_local >= p.ni_tiles * (ITILE / 2)) return;
+    const int64_t it = pair_local / (ITILE / 2);
+    const int q = pair_local - (int)it * (ITILE / 2);
+    const TileOwners o = tile_owners(p.ni_tiles, p.nj_tiles, grid_main, it);
+    if (!o.split) return;   // finished inside the force kernel
+    const int64_t U = (int64_t)p.ni_tiles * p.nj_tiles;
+    float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0;
+    for (int c = o.first; c <= o.last; ++c) {   // fixed order: bit-reproducible
+        if (cta_unit_begin(U, grid_main, c) >= cta_unit_begin(U, grid_main, c + 1)) continue;   // idle CTA
+        const int slot = partial_slot(p.ni_tiles, p.nj_tiles, grid_main, c, it);
+        const float4* src = p.partial + ((size_t)c * 2 + slot) * ITILE + 2 * q;
+        const float4 s0 = src[0], s1 = src[1];
+        a0.x += s0.x; a0.y += s0.y; a0.z += s0.z;
+        a1.x += s1.x; a1.y += s1.y; a1.z += s1.z;
+    }
+    finish_pair(p, pair_local, a0, a1);
+}
+
+// ------------------------------------------------------------------------------------------------
+// dispatch
+// ------------------------------------------------------------------------------------------------
+int variant_bodies_per_thread(int variant) {
+    switch (variant) {
+        case 1: case 2: return 4;
+        case 3: case 4: return 8;
+        case 5: return 2;
+        case 6: return 6;
+        default: return 0;
+    }
+}
+
+size_t force_smem_bytes() { return kSmemBytes; }
+
+typedef void (*ForceKernel)(const StepParams);
+static ForceKernel pick_force(int variant, int cut) {
+#define GS_PICK(R, PK) (cut == kCutoff ? (ForceKernel)force_step_kernel<R, kCutoff, PK> \
+                                       : (ForceKernel)force_step_kernel<R, kSoftened, PK>)
+    switch (variant) {
+        case 1: return GS_PICK(4, true);
+        case 2: return GS_PICK(4, false);
+        case 3: return GS_PICK(8, true);
+        case 4: return GS_PICK(8, false);
+        case 5: return GS_PICK(2, true);
+        case 6: return GS_PICK(6, true);
+        default: return nullptr;
+    }
+#undef GS_PICK
+}
+
+cudaError_t force_kernel_occupancy(int variant, int cut_mode, int* ctas_per_sm, int* regs) {
+    ForceKernel k = pick_force(variant, cut_mode);
+    if (!k) return cudaErrorInvalidValue;
+    cudaError_t e = cudaFuncSetAttribute((const void*)k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
+    if (e != cudaSuccess) return e;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(ctas_per_sm, (const void*)k, kThreads, kSmemBytes);
+    if (e != cudaSuccess) return e;
+    cudaFuncAttributes fa;
+    e = cudaFuncGetAttributes(&fa, (const void*)k);
+    if (e != cudaSuccess) return e;
+    *regs = fa.numRegs;
+    return cudaSuccess;
+}
+
+cudaError_t launch_force(int variant, int cut_mode, const StepParams& p, int grid, cudaStream_t s) {
+    ForceKernel k = pick_force(variant, cut_mode);
+    if (!k) return cudaErrorInvalidValue;
+    k<<<grid, kThreads, kSmemBytes, s>>>(p);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_fixup(int variant, const StepParams& p, int grid_main, cudaStream_t s) {
+    const int R = variant_bodies_per_thread(variant);
+    const int pairs = p.ni_tiles * (kThreads * R / 2);
+    const int blocks = (pairs + 255) / 256;
+    switch (R) {
+        case 2: fixup_kernel<2><<<blocks, 256, 0, s>>>(p, grid_main); break;
+        case 4: fixup_kernel<4><<<blocks, 256, 0, s>>>(p, grid_main); break;
+        case 6: fixup_kernel<6><<<blocks, 256, 0, s>>>(p, grid_main); break;
+        case 8: fixup_kernel<8><<<blocks, 256, 0, s>>>(p, grid_main); break;
+        default: return cudaErrorInvalidValue;
+    }
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------------
+// AoS <-> packed pairs
+// ------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void aos_to_packed_kernel(const T* __restrict__ aos, int n, int n_pad, double G, float4* pos,
+                                     float4* vel_local, double* mass, int i_begin, int n_local_pad) {
+    const int pair = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pair >= n_pad / 2) return;
+    float x[2], y[2], z[2], vx[2], vy[2], vz[2], mu[2];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        const int i = 2 * pair + h;
+        if (i < n) {
+            const T* r = aos + (size_t)i * 7;
+            x[h] = (float)r[0]; y[h] = (float)r[1]; z[h] = (float)r[2];
+            vx[h] = (float)r[3]; vy[h] = (float)r[4]; vz[h] = (float)r[5];
+            const double m = (double)r[6];
+            mu[h] = (float)(G * m);          // never form m_i*m_j: G*m <= 1.33e20 fits fp32
+            mass[i] = m;
+        } else {                             // padding: massless, at the origin, at rest
+            x[h] = y[h] = z[h] = vx[h] = vy[h] = vz[h] = mu[h] = 0.f;
+            mass[i] = 0.0;
+        }
+    }
+    pos[2 * pair] = make_float4(x[0], x[1], y[0], y[1]);
+    pos[2 * pair + 1] = make_float4(z[0], z[1], mu[0], mu[1]);
+    const int first = 2 * pair;
+    if (first >= i_begin && first < i_begin + n_local_pad) {
+        const int pl = (first - i_begin) >> 1;
+        vel_local[2 * pl] = make_float4(vx[0], vx[1], vy[0], vy[1]);
+        vel_local[2 * pl + 1] = make_float4(vz[0], vz[1], 0.f, 0.f);
+    }
+}
+
+template <typename T>
+__global__ void packed_to_aos_kernel(const float4* __restrict__ pos, const float4* __restrict__ vel,
+                                     const double* __restrict__ mass, int n, T* aos) {
+    const int pair = blockIdx.x * blockDim.x + threadIdx.x;
+    if (2 * pair >= n) return;
+    const float4 PA = pos[2 * pair], PB = pos[2 * pair + 1];
+    const float4 VA = vel[2 * pair], VB = vel[2 * pair + 1];
+    {
+        T* r = aos + (size_t)(2 * pair) * 7;
+        r[0] = (T)PA.x; r[1] = (T)PA.z; r[2] = (T)PB.x;
+        r[3] = (T)VA.x; r[4] = (T)VA.z; r[5] = (T)VB.x;
+        r[6] = (T)mass[2 * pair];
+    }
+    if (2 * pair + 1 < n) {
+        T* r = aos + (size_t)(2 * pair + 1) * 7;
+        r[0] = (T)PA.y; r[1] = (T)PA.w; r[2] = (T)PB.y;
+        r[3] = (T)VA.y; r[4] = (T)VA.w; r[5] = (T)VB.y;
+        r[6] = (T)mass[2 * pair + 1];
+    }
+}
+
+cudaError_t launch_aos_to_packed(const void* aos, int record_bytes, int n, int n_pad, double G, float4* pos,
+                                 float4* vel_local, double* mass, int i_begin, int n_local_pad,
+                                 cudaStream_t s) {
+    const int blocks = (n_pad / 2 + 255) / 256;
+    if (record_bytes == 28)
+        aos_to_packed_kernel<float><<<blocks, 256, 0, s>>>((const float*)aos, n, n_pad, G, pos, vel_local, mass,
+                                                           i_begin, n_local_pad);
+    else if (record_bytes == 56)
+        aos_to_packed_kernel<double><<<blocks, 256, 0, s>>>((const double*)aos, n, n_pad, G, pos, vel_local, mass,
+                                                            i_begin, n_local_pad);
+    else
+        return cudaErrorInvalidValue;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_packed_to_aos(const float4* pos, const float4* vel_full, const double* mass, int n, void* aos,
+                                 int record_bytes, cudaStream_t s) {
+    const int blocks = ((n + 1) / 2 + 255) / 256;
+    if (record_bytes == 28)
+        packed_to_aos_kernel<float><<<blocks, 256, 0, s>>>(pos, vel_full, mass, n, (float*)aos);
+    else if (record_bytes == 56)
+        packed_to_aos_kernel<double><<<blocks, 256, 0, s>>>(pos, vel_full, mass, n, (double*)aos);
+    else
+        return cudaErrorInvalidValue;
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------------
+// energy diagnostics (not in the reference)
+// ------------------------------------------------------------------------------------------------
+constexpr int kEThreads = 256;
+
+__device__ __forceinline__ double block_sum(double v, double* red) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    const int w = threadIdx.x >> 5;
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) red[w] = v;
+    __syncthreads();
+    double t = 0.0;
+    if (threadIdx.x == 0)
+        for (int i = 0; i < kEThreads / 32; ++i) t += red[i];
+    return t;   // valid in thread 0
+}
+
+// One i-body per thread against every j-tile; fp32 pair terms, a 64-term fp32 partial, fp64 above.
+__global__ void __launch_bounds__(kEThreads) potential_kernel(const float4* __restrict__ pos, int n_pad, int i_begin,
+                                                              float eps2, float cut2, double* out_partials) {
+    __shared__ float4 tile[kJTile];
+    __shared__ double red[kEThreads / 32];
+    const int i = i_begin + blockIdx.x * kEThreads + threadIdx.x;
+    const float4 IA = pos[2 * (i >> 1)], IB = pos[2 * (i >> 1) + 1];
+    const bool odd = (i & 1) != 0;
+    const float xi = odd ? IA.y : IA.x, yi = odd ? IA.w : IA.z, zi = odd ? IB.y : IB.x, mui = odd ? IB.w : IB.z;
+    double pot = 0.0;
+    for (int j0 = 0; j0 < n_pad; j0 += kJTile) {
+        __syncthreads();
+        for (int t = threadIdx.x; t < kJTile; t += kEThreads) tile[t] = pos[j0 + t];
+        __syncthreads();
+        for (int c = 0; c < kJTile / 2; c += 32) {
+            float part = 0.f;
+#pragma unroll 4
+            for (int jp = c; jp < c + 32; ++jp) {
+                const float4 A = tile[2 * jp], B = tile[2 * jp + 1];
+                const int j = j0 + 2 * jp;
+                {
+                    const float dx = A.x - xi, dy = A.z - yi, dz = B.x - zi;
+                    const float d2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
+                    const float ri = rsqrt_approx(d2 + eps2);
+                    part += (j != i && d2 >= cut2) ? B.z * ri : 0.f;
+                }
+                {
+                    const float dx = A.y - xi, dy = A.w - yi, dz = B.y - zi;
+                    const float d2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
+                    const float ri = rsqrt_approx(d2 + eps2);
+                    part += (j + 1 != i && d2 >= cut2) ? B.w * ri : 0.f;
+                }
+            }
+            pot += (double)part;
+        }
+    }
+    const double total = block_sum(pot * (double)mui, red);
+    if (threadIdx.x == 0) out_partials[blockIdx.x] = total;
+}
+
+__global__ void __launch_bounds__(kEThreads) kinetic_kernel(const float4* __restrict__ vel_local,
+                                                            const double* __restrict__ mass, int i_begin,
+                                                            double* out4) {
+    __shared__ double red[kEThreads / 32];
+    const int il = blockIdx.x * kEThreads + threadIdx.x;   // local body
+    const float4 VA = vel_local[2 * (il >> 1)], VB = vel_local[2 * (il >> 1) + 1];
+    const bool odd = (il & 1) != 0;
+    const double vx = odd ? VA.y : VA.x, vy = odd ? VA.w : VA.z, vz = odd ? VB.y : VB.x;
+    const double m = mass[i_begin + il];
+    const double e = block_sum(m * (vx * vx + vy * vy + vz * vz), red);
+    const double px = block_sum(m * vx, red);
+    const double py = block_sum(m * vy, red);
+    const double pz = block_sum(m * vz, red);
+    if (threadIdx.x == 0) {
+        out4[4 * blockIdx.x + 0] = e; out4[4 * blockIdx.x + 1] = px;
+        out4[4 * blockIdx.x + 2] = py; out4[4 * blockIdx.x + 3] = pz;
+    }
+}
+
+int energy_grid(int n_local_pad) { return n_local_pad / kEThreads; }
+
+cudaError_t launch_potential(const float4* pos, int n_pad, int i_begin, int n_local_pad, float eps2, float cut2,
+                             double* out_partials, cudaStream_t s) {
+    potential_kernel<<<energy_grid(n_local_pad), kEThreads, 0, s>>>(pos, n_pad, i_begin, eps2, cut2, out_partials);
+    return cudaGetLastError();
+}
+cudaError_t launch_kinetic(const float4* vel_local, const double* mass, int i_begin, int n_local_pad, double* out4,
+                           cudaStream_t s) {
+    kinetic_kernel<<<energy_grid(n_local_pad), kEThreads, 0, s>>>(vel_local, mass, i_begin, out4);
+    return cudaGetLastError();
+}
+
+}  // namespace gs

@@ -1,0 +1,67 @@
+// gs_kernels.h -- launch wrappers of the sm_100a kernels (gs_kernels.cu) used by the C-ABI (gs_api.cu).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "gs_layout.h"
+
+namespace gs {
+
+enum FinalMode : int { kFinalIntegrate = 0,   // v += a*kick_dt; x += v*drift_dt -> pos_new
+                       kFinalAccOut = 1,      // write accelerations, state untouched
+                       kFinalKickOnly = 2 };  // v += a*kick_dt only (leapfrog velocity synchronisation)
+enum CutMode : int { kSoftened = 0, kCutoff = 1 };   // eps > 0  /  eps == 0 (reference r<1e-10 rule)
+
+// Kernel variants (gs_config.variant / env GRAVSIM_VARIANT). R = i-bodies per thread.
+//   1: R=4 packed f32x2 (default)   2: R=4 scalar   3: R=8 packed   4: R=8 scalar   5: R=2 packed
+//   6: R=6 packed
+constexpr int kNumVariants = 6;
+constexpr int kDefaultVariant = 1;
+int variant_bodies_per_thread(int variant);           // 0 if the variant does not exist
+inline int variant_i_tile(int variant) { return kThreads * variant_bodies_per_thread(variant); }
+
+struct StepParams {
+    const float4* pos_old;   // packed pairs, n_pad bodies (all ranks' bodies)
+    float4* pos_new;         // packed pairs, n_pad bodies; only this rank's slice is written
+    float4* vel;             // packed pairs, this rank's slice only (local index)
+    const float4* acc_in;    // optional: accelerations to add before finishing (local index)
+    float4* acc_out;         // kFinalAccOut: accelerations (x,y,z,0) per local body
+    float4* partial;         // scratch [grid][2][i_tile]: partial sums of split i-tiles
+    int n;                   // real bodies; bodies >= n are padding and are never moved
+    int i_begin;             // first body of this rank's slice (global index, multiple of kPadBodies)
+    int ni_tiles;            // i-tiles in this rank's slice
+    int nj_tiles;            // j-tiles covered by this launch (virtual index v in [0,nj_tiles))
+    int nj_total;            // n_pad / kJTile
+    int j_rot;               // physical j-tile = (v + j_rot) mod nj_total
+    float eps2;              // softening^2 (kSoftened) or 0
+    float cut2;              // kCutoff: pairs with r^2 < cut2 contribute nothing (1e-20)
+    float kick_dt;           // v += a * kick_dt
+    float drift_dt;          // x += v_new * drift_dt
+    int final_mode;          // FinalMode
+};
+
+size_t force_smem_bytes();
+// Max resident CTAs per SM of the force kernel for this variant / cut mode, and its registers.
+cudaError_t force_kernel_occupancy(int variant, int cut_mode, int* ctas_per_sm, int* regs);
+cudaError_t launch_force(int variant, int cut_mode, const StepParams& p, int grid, cudaStream_t s);
+// Finishes the i-tiles whose units were split across CTAs (sums the partials, then integrates
+// or writes accelerations).  `grid_main` is the force kernel's grid.
+cudaError_t launch_fixup(int variant, const StepParams& p, int grid_main, cudaStream_t s);
+
+// AoS <-> packed-pair conversion on the device. `aos` is the raw byte image of the reference's
+// 28-byte (f32) or 56-byte (f64) records.  Bodies >= n are padding (mu = 0, at the origin).
+cudaError_t launch_aos_to_packed(const void* aos, int record_bytes, int n, int n_pad, double G,
+                                 float4* pos, float4* vel_local, double* mass, int i_begin,
+                                 int n_local_pad, cudaStream_t s);
+cudaError_t launch_packed_to_aos(const float4* pos, const float4* vel_full, const double* mass,
+                                 int n, void* aos, int record_bytes, cudaStream_t s);
+
+// Energy diagnostics (fp64 accumulation).  potential: out_partials[gridDim] doubles, one per
+// CTA, of sum_i mu_i * sum_{j != i} mu_j / sqrt(r^2 + eps^2) over this rank's i-bodies (the caller
+// sums them and multiplies by -1/(2G)).  kinetic: out4[grid*4] = {sum m v^2, sum m vx, m vy, m vz}.
+int energy_grid(int n_local_pad);
+cudaError_t launch_potential(const float4* pos, int n_pad, int i_begin, int n_local_pad,
+                             float eps2, float cut2, double* out_partials, cudaStream_t s);
+cudaError_t launch_kinetic(const float4* vel_local, const double* mass, int i_begin, int n_local_pad,
+                           double* out4, cudaStream_t s);
+
+}  // namespace gs

@@ -1,0 +1,41 @@
+"""Exploration tool (not the bench): wall-clock rate of gs_step per kernel variant / mode / N."""
+import os
+import sys
+import time
+
+import numpy as np
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from __graft_entry__ import load_package  # noqa: E402
+
+gs = load_package()
+PEAK = 148 * 128 * 2 * 1.965e9
+
+
+def probe(n, variant, eps, steps=4, grid=None):
+    b = gs.ic_plummer(n, seed=1) if eps > 0 else gs.ic_reference_uniform(n, seed=1)
+    if grid:
+        os.environ["GRAVSIM_GRID"] = str(grid)
+    else:
+        os.environ.pop("GRAVSIM_GRID", None)
+    with gs.GravSim(n, dt=1e-3 if eps > 0 else 3600.0, G=1.0 if eps > 0 else gs.G_SI, eps=eps, variant=variant) as sim:
+        sim.upload(b)
+        sim.step(2)
+        sim.sync()
+        t0 = time.perf_counter()
+        sim.step(steps)
+        sim.sync()
+        dt = (time.perf_counter() - t0) / steps
+        info = sim.info
+    rate = n * (n - 1.0) / dt
+    print(f"N={n:8d} variant={variant} mode={'soft' if eps > 0 else 'cut '} grid={info.grid} regs={info.regs_per_thread} "
+          f"{dt * 1e3:9.3f} ms/step  {rate:.3e} int/s  {rate * 20 / PEAK * 100:5.1f}% of 74.5 TF", flush=True)
+
+
+if __name__ == "__main__":
+    ns = [int(x) for x in sys.argv[1].split(",")] if len(sys.argv) > 1 else [262144]
+    variants = [int(x) for x in sys.argv[2].split(",")] if len(sys.argv) > 2 else [1, 2, 3, 4, 5, 6]
+    for n in ns:
+        for v in variants:
+            for eps in (0.01, 0.0):
+                probe(n, v, eps)
