@@ -419,6 +419,9 @@ int gs_step(gs_ctx* c, int nsteps) {
         if (c->cfg.integrator == GS_INTEGRATOR_LEAPFROG) c->vel_synced = false;
         c->steps_done++;
     }
+    // order the last exchange on the caller-visible stream too, so an event recorded there after
+    // gs_step covers every byte of the step (positions are then valid on every rank)
+    if (c->cfg.world_size > 1 && nsteps > 0) GS_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_gather[c->cur], 0));
     return GS_OK;
 }
 
