@@ -3,7 +3,8 @@
 
 Workload (BASELINE.json configs[2], the configuration the metric is quoted on): N = 1,048,576-body
 Plummer sphere in N-body units (G = 1, M = 1, a = 1, equal masses), softening eps = 0.01,
-dt = 1/256, kick-drift-kick leapfrog; one "step" = one full time step = N*(N-1) ordered
+dt = 1/256, the reference's own integrator (v += a dt; x += v dt: cuda.cu:73-76, mpi.c:206-215,
+i.e. symplectic Euler == leapfrog with velocities read half a step apart); one "step" = one full time step = N*(N-1) ordered
 interactions (force pass + fused integration + position exchange when N_gpus > 1).
 
     python bench.py [--gpus N] [--steps K] [--warmup W]          # our CUDA path
@@ -39,11 +40,21 @@ UNIT = "interactions/s"
 
 
 def workload_config(n_gpus):
-    return {"workload": "plummer_n1048576_leapfrog", "n_bodies": N_BODIES, "eps": EPS, "dt": DT, "G": 1.0,
-            "integrator": "leapfrog-kdk", "interactions_per_step": N_BODIES * (N_BODIES - 1),
+    return {"workload": "plummer_n1048576_euler", "n_bodies": N_BODIES, "eps": EPS, "dt": DT, "G": 1.0,
+            "integrator": "symplectic-euler (reference: cuda.cu:73-76, mpi.c:206-215)", "interactions_per_step": N_BODIES * (N_BODIES - 1),
             "partition": f"{n_gpus} x N/{n_gpus} i-bodies, NCCL all-gather of float4 positions per step"
             if n_gpus > 1 else "single GPU",
             "l2": "flushed between timed steps (256 MiB write); positions 16 MiB"}
+
+
+def traffic_bytes(n, world):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one force-kernel launch, from the committed ncu
+    --set full capture of this same workload (profiles/force_kernel_traffic.json); None otherwise."""
+    try:
+        t = json.load(open(os.path.join(REPO, "profiles", "force_kernel_traffic.json")))
+        return t["dram_traffic_bytes_per_launch"] if (n == N_BODIES and world == 1) else None
+    except Exception:       # noqa: BLE001
+        return None
 
 
 def measured_peaks():
@@ -205,9 +216,10 @@ def main():
     bodies = gs.ic_plummer(n, seed=2024)                      # identical on every rank (seeded)
     pinned_in = torch.from_numpy(bodies).pin_memory()
     pinned_out = torch.empty_like(pinned_in).pin_memory()
-    stream = torch.cuda.current_stream()
+    stream = torch.cuda.Stream()               # the library launches on THIS stream; events are recorded on it
+    torch.cuda.set_stream(stream)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
-    sim = gs.GravSim(n, dt=DT, G=1.0, eps=EPS, integrator=gs.INTEGRATOR_LEAPFROG, device=local_rank,
+    sim = gs.GravSim(n, dt=DT, G=1.0, eps=EPS, integrator=gs.INTEGRATOR_EULER, device=local_rank,
                      rank=rank, world_size=world, nccl_id=nccl_id, stream=stream.cuda_stream)
     sim.upload_ptr(pinned_in.data_ptr(), n)
 
@@ -264,13 +276,13 @@ def main():
         per_gpu_rate = value / world
         ach_tf = per_gpu_rate * FLOP_PER_INTERACTION / 1e12
         roof = {"bound": "fp32", "achieved": ach_tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": ach_tf / peak_tf,
-                "traffic": None,
+                "traffic": traffic_bytes(n, world),
                 "note": f"CUDA-core FP32 FMA roofline ({sms} SMs x 128 lanes x 2 x {sm_max:.0f} MHz from MEASURED_PEAKS.json "
                         "sm_max_mhz; the file holds no FP32 figure): the interaction is not a dense contraction, so neither "
                         "the HBM nor the tensor roofline bounds it. achieved = 20 flop x N*(N-1)/n_gpus interactions per "
                         "force-kernel launch / CUDA-event step time (force kernel >99.9% of the step, profiles/).",
-                "hbm_gbs_algorithmic": (64.0 * n / world + 16.0 * n) / (ms_total / args.steps * 1e-3) / 1e9,
-                "issue_slot_ceiling_frac": 20.0 / 24.0}
+                "algorithmic_bytes_per_launch": 64.0 * n / world + 16.0 * n,
+                "fma_pipe_ceiling_frac": 20.0 / 24.0}
         if clocks and clocks.get("sm_mhz"):
             roof["frac_at_measured_clock"] = ach_tf / (sms * 128 * 2 * clocks["sm_mhz"] * 1e6 / 1e12)
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
