@@ -25,7 +25,7 @@ NCCL_ID_BYTES = 128
 EXPORTED_SYMBOLS = [
     "gs_config_init", "gs_create", "gs_destroy", "gs_nccl_unique_id",
     "gs_upload_aos_f32", "gs_upload_aos_f64", "gs_download_aos_f32", "gs_download_aos_f64",
-    "gs_step", "gs_accel", "gs_energy", "gs_sync", "gs_set_dt",
+    "gs_step", "gs_accel", "gs_energy", "gs_potential_energy_noalloc", "gs_sync", "gs_set_dt",
     "gs_get_info", "gs_kernel_launches", "gs_last_cuda_error", "gs_strerror", "gs_version",
     "gs_host_alloc", "gs_host_free",
     "gs_plan_slice", "gs_plan_cta_range", "gs_plan_tile_owners", "gs_plan_tiles",
@@ -115,6 +115,7 @@ def lib():
     L.gs_accel.argtypes = [C.c_void_p, C.c_void_p]
     L.gs_energy.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double)]
     L.gs_sync.argtypes = [C.c_void_p]
+    L.gs_potential_energy_noalloc.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_double, C.c_void_p, C.c_void_p]
     L.gs_set_dt.argtypes = [C.c_void_p, C.c_double]
     L.gs_get_info.argtypes = [C.c_void_p, C.POINTER(GsInfo)]
     L.gs_nccl_unique_id.argtypes = [C.c_void_p]
@@ -246,6 +247,17 @@ def dump_positions_mpi_format(path, records56):
         _check(lib().gs_dump_positions_mpi_format(f, r.ctypes.data, r.shape[0]), "dump")
     finally:
         libc.fclose(f)
+
+
+NOALLOC_MAX_BODIES = 4194304
+
+
+def potential_energy_noalloc(pos_packed_ptr, n_pad, G, eps, potential_ptr, stream=0):
+    """gs_potential_energy_noalloc on caller-owned device memory (raw pointers); allocates nothing.
+    Enqueues on `stream` and returns; read *potential_ptr after synchronising that stream."""
+    _check(lib().gs_potential_energy_noalloc(C.c_void_p(pos_packed_ptr), int(n_pad), float(G), float(eps),
+                                             C.c_void_p(potential_ptr), C.c_void_p(stream)),
+           "gs_potential_energy_noalloc")
 
 
 # ---- the engine -----------------------------------------------------------------------------------

@@ -170,6 +170,7 @@ const char* gs_strerror(int code) {
         case GS_ESTATE: return "call out of order";
         case GS_ENOGPU: return "no CUDA device available (libgravsim has no CPU path)";
         case GS_EIO: return "state-file I/O error";
+        case GS_ETOOBIG: return "problem exceeds a fixed-size buffer (gs_potential_energy_noalloc: at most 4194304 padded bodies)";
         default: return "unknown error";
     }
 }

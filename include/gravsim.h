@@ -37,6 +37,7 @@ extern "C" {
 #define GS_ESTATE   -5   /* call out of order (e.g. step before upload)            */
 #define GS_ENOGPU   -6   /* no CUDA device: this library has no CPU path           */
 #define GS_EIO      -7   /* state-file I/O failed                                  */
+#define GS_ETOOBIG  -8   /* problem larger than a fixed-size buffer allows         */
 
 #define GS_G_SI 6.67430e-11          /* cuda.cu:11, mpi.c:9, pyspark.py:46 */
 #define GS_NCCL_ID_BYTES 128
@@ -121,6 +122,25 @@ int gs_accel(gs_ctx *ctx, float *acc3_host);
 /* Kinetic, potential energy and linear momentum (fp64 accumulation).  Not in the reference.
  * Collective when world_size > 1 (every rank gets the global values). */
 int gs_energy(gs_ctx *ctx, double *kinetic, double *potential, double momentum[3]);
+
+/* Potential energy WITHOUT any allocation and without a gs_ctx.  (No counterpart in the reference:
+ * it computes no energies and allocates as it pleases, cuda.cu:145-149,159.)
+ * For callers that may not call cudaMalloc -- a hook inside a loop whose device memory comes from a
+ * pool or a caching allocator, a latency-critical loop that cannot afford cudaMalloc's device-wide
+ * synchronisation, a process at its memory limit.  The kernel's per-CTA partial sums go to a fixed
+ * 128 KiB __device__ array inside the library (present on every GPU that loads it, until exit)
+ * instead of a cudaMalloc'ed buffer, hence:
+ *   - n_pad <= GS_NOALLOC_MAX_BODIES, else GS_ETOOBIG and nothing is launched;
+ *   - every call on a GPU shares that array: calls that can overlap on the GPU (two streams, two
+ *     threads) race and must be serialised by the caller; stale contents are never read;
+ *   - the first call on each device resolves the array's address; make it before any stream capture.
+ * pos_packed_dev: n_pad bodies in the packed-pair layout of DESIGN.md section 3, caller-owned device
+ * memory ({x0,x1,y0,y1},{z0,z1,mu0,mu1} per pair, mu = (float)(G*mass); bodies beyond the real ones
+ * all-zero); n_pad a multiple of 512.  potential_dev: one double in device memory, written on
+ * `stream` (a cudaStream_t, NULL = default stream); same value as gs_energy()'s potential. */
+#define GS_NOALLOC_MAX_BODIES 4194304
+int gs_potential_energy_noalloc(const void *pos_packed_dev, int n_pad, double G, double eps,
+                                double *potential_dev, void *stream);
 
 int gs_sync(gs_ctx *ctx);              /* cudaDeviceSynchronize at cuda.cu:157, per ctx */
 int gs_set_dt(gs_ctx *ctx, double dt);
