@@ -200,11 +200,8 @@ def main():
     nccl_id = None
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-        idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
-        if rank == 0:
-            idt.copy_(torch.frombuffer(bytearray(gs.nccl_unique_id()), dtype=torch.uint8))
-        dist.broadcast(idt, 0)
-        nccl_id = bytes(idt.cpu().numpy().tobytes())
+        from gravsim_b200 import dist as gdist
+        nccl_id = gdist.broadcast_bytes(gs.nccl_unique_id() if rank == 0 else None, 128, device="cuda")
 
     def barrier():
         torch.cuda.synchronize()

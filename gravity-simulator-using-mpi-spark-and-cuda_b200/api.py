@@ -19,6 +19,7 @@ INTEGRATOR_LEAPFROG = 1
 G_SI = 6.67430e-11          # cuda.cu:11, mpi.c:9
 FLAG_NO_OVERLAP = 1
 FLAG_TWO_PASS = 2
+FLAG_NO_UNIFORM_MASS = 4
 NCCL_ID_BYTES = 128
 
 # every symbol include/gravsim.h declares (checked by the CPU tests)

@@ -16,7 +16,8 @@ struct gs_ctx {
     gs_config cfg;
     int device = 0;
     int n = 0, n_pad = 0, slice = 0, i_begin = 0;   // slice = padded bodies per rank
-    int variant = 0, R = 0, i_tile = 0, cut_mode = 0;
+    int variant = 0, R = 0, threads = 0, i_tile = 0, cut_mode = 0;
+    float mu_uniform = 0.f;       // != 0: all real bodies share this G*m (hoisted-mass kernel)
     int sm_count = 0, ctas_per_sm = 0, grid = 0, regs = 0;
     float eps2 = 0.f, cut2 = 0.f;
     float4* pos[2] = {nullptr, nullptr};
@@ -91,6 +92,7 @@ int force_pass(gs_ctx* c, int final_mode, float kick, float drift, float4* acc_o
     p.cut2 = c->cut2;
     p.kick_dt = kick;
     p.drift_dt = drift;
+    p.mu_uniform = c->mu_uniform;
     const int W = c->cfg.world_size;
     // two passes: multi-GPU overlap, or GS_FLAG_TWO_PASS (same code path on one GPU, for tests)
     const bool two_pass = ((W > 1) && !(c->cfg.flags & GS_FLAG_NO_OVERLAP)) ||
@@ -149,6 +151,19 @@ int sync_velocities(gs_ctx* c) {
     return GS_OK;
 }
 
+// Measured on B200 at N = 1M (profiles/r2_variant_sweep_*.txt): softened -> R=6 x 256 threads (72.0 % general,
+// 78.7 % equal masses), cutoff -> R=8 x 256 threads (65.2 %).  R=6 has a 1536-body i-tile, which pads some
+// N / GPU-count combinations more than the 2048-body tile of R=8 does: charge each its padded work.
+int default_variant(int n, int world, int cut_mode) {
+    if (cut_mode == kCutoff) return 3;
+    int pad6 = 0, pad3 = 0;
+    if (gs_plan_slice(n, world, 0, 6, &pad6, nullptr, nullptr) != GS_OK ||
+        gs_plan_slice(n, world, 0, 3, &pad3, nullptr, nullptr) != GS_OK)
+        return kDefaultVariant;
+    const double cost6 = (double)pad6 * pad6, cost3 = (double)pad3 * pad3 / 0.98;
+    return cost6 <= cost3 ? 6 : 3;
+}
+
 int set_device(gs_ctx* c) {
     GS_CUDA(c, cudaSetDevice(c->device));
     return GS_OK;
@@ -190,9 +205,9 @@ void gs_config_init(gs_config* cfg) {
 
 int gs_plan_tiles(int variant, int* i_tile, int* j_tile) {
     if (variant == 0) variant = kDefaultVariant;
-    const int R = variant_bodies_per_thread(variant);
-    if (R == 0) return GS_EINVAL;
-    if (i_tile) *i_tile = kThreads * R;
+    VariantInfo vi;
+    if (!variant_info(variant, &vi)) return GS_EINVAL;
+    if (i_tile) *i_tile = vi.i_tile;
     if (j_tile) *j_tile = kJTile;
     return GS_OK;
 }
@@ -200,10 +215,10 @@ int gs_plan_tiles(int variant, int* i_tile, int* j_tile) {
 int gs_plan_slice(int n, int world_size, int rank, int variant, int* n_pad, int* i_begin_pad, int* i_end_pad) {
     if (n <= 0 || world_size < 1 || rank < 0 || rank >= world_size) return GS_EINVAL;
     if (variant == 0) variant = kDefaultVariant;
-    const int R = variant_bodies_per_thread(variant);
-    if (R == 0) return GS_EINVAL;
+    VariantInfo vi;
+    if (!variant_info(variant, &vi)) return GS_EINVAL;
     // every rank's slice is a whole number of i-tiles and of j-tiles
-    int64_t tile = (int64_t)kThreads * R;
+    int64_t tile = vi.i_tile;
     int64_t unit = tile;
     while (unit % kJTile != 0) unit += tile;
     unit *= world_size;
@@ -299,14 +314,17 @@ int gs_create(gs_ctx** out, const gs_config* cfg) {
     if (prop.major < 10) return fail(GS_ENOGPU);   // sm_100a code only
     c->sm_count = prop.multiProcessorCount;
 
+    c->cut_mode = (cfg->eps > 0.0) ? kSoftened : kCutoff;
     c->variant = cfg->variant;
     if (c->variant == 0) {
         const char* ev = getenv("GRAVSIM_VARIANT");
-        c->variant = ev ? atoi(ev) : kDefaultVariant;
+        c->variant = ev ? atoi(ev) : default_variant(cfg->n, cfg->world_size, c->cut_mode);
     }
-    c->R = variant_bodies_per_thread(c->variant);
-    if (c->R == 0) return fail(GS_EINVAL);
-    c->i_tile = kThreads * c->R;
+    VariantInfo vi;
+    if (!variant_info(c->variant, &vi)) return fail(GS_EINVAL);
+    c->R = vi.R;
+    c->threads = vi.threads;
+    c->i_tile = vi.i_tile;
     c->cut_mode = (cfg->eps > 0.0) ? kSoftened : kCutoff;
     c->eps2 = (float)(cfg->eps * cfg->eps);
     c->cut2 = (c->cut_mode == kCutoff) ? 1e-20f : 0.f;   // (1e-10)^2: cuda.cu:39, mpi.c:64
@@ -317,8 +335,12 @@ int gs_create(gs_ctx** out, const gs_config* cfg) {
     c->i_begin = ib;
     c->slice = ie - ib;
 
-    cudaError_t e = force_kernel_occupancy(c->variant, c->cut_mode, &c->ctas_per_sm, &c->regs);
-    if (e != cudaSuccess || c->ctas_per_sm < 1) { c->last_cuda_error = (int)e; return fail(GS_ECUDA); }
+    // both flavours of the kernel (general / hoisted uniform mass) must fit the same persistent grid
+    int ctas_u = 0, regs_u = 0;
+    cudaError_t e = force_kernel_occupancy(c->variant, c->cut_mode, false, &c->ctas_per_sm, &c->regs);
+    if (e == cudaSuccess) e = force_kernel_occupancy(c->variant, c->cut_mode, true, &ctas_u, &regs_u);
+    if (e != cudaSuccess || c->ctas_per_sm < 1 || ctas_u < 1) { c->last_cuda_error = (int)e; return fail(GS_ECUDA); }
+    if (ctas_u < c->ctas_per_sm) c->ctas_per_sm = ctas_u;
     c->grid = c->sm_count * c->ctas_per_sm;
     const char* eg = getenv("GRAVSIM_GRID");
     if (eg && atoi(eg) > 0 && atoi(eg) <= c->grid) c->grid = atoi(eg);
@@ -380,6 +402,25 @@ static int upload_common(gs_ctx* c, const void* host, int n, int record_bytes) {
     const size_t bytes = (size_t)n * record_bytes;
     if ((rc = ensure_aos(c, bytes)) != GS_OK) return rc;
     GS_CUDA(c, cudaMemcpyAsync(c->d_aos, host, bytes, cudaMemcpyHostToDevice, c->stream));
+    // equal masses (Plummer spheres, cosmological particles): the mass factor leaves the inner loop
+    c->mu_uniform = 0.f;
+    if (!(c->cfg.flags & GS_FLAG_NO_UNIFORM_MASS)) {
+        bool same = true;
+        double m0;
+        if (record_bytes == 28) {
+            const char* b = (const char*)host;
+            float f0, f;
+            memcpy(&f0, b + 24, 4);
+            for (int i = 1; i < n && same; ++i) { memcpy(&f, b + (size_t)i * 28 + 24, 4); same = (f == f0); }
+            m0 = f0;
+        } else {
+            const double* d = (const double*)host;
+            m0 = d[6];
+            for (int i = 1; i < n && same; ++i) same = (d[(size_t)i * 7 + 6] == m0);
+        }
+        const float mu = (float)(c->cfg.G * m0);
+        if (same && mu > 0.f && std::isfinite(mu)) c->mu_uniform = mu;
+    }
     c->cur = 0;
     GS_CUDA(c, launch_aos_to_packed(c->d_aos, record_bytes, n, c->n_pad, c->cfg.G, c->pos[0], c->vel, c->mass,
                                     c->i_begin, c->slice, c->stream));
@@ -551,7 +592,7 @@ int gs_get_info(const gs_ctx* c, gs_info* info) {
     info->sm_count = c->sm_count; info->grid = c->grid;
     info->i_tile = c->i_tile; info->j_tile = kJTile;
     info->stages = kStages; info->variant = c->variant;
-    info->regs_per_thread = c->regs; info->threads = kThreads;
+    info->regs_per_thread = c->regs; info->threads = c->threads;
     info->scratch_bytes = (int64_t)c->partial_bytes;
     return GS_OK;
 }

@@ -110,14 +110,16 @@ struct Acc {
 
 // One j-tile against this thread's R i-bodies, packed f32x2: per j-PAIR and i-body
 //   3 FADD2 + 3 FFMA2 + 2 MUFU.RSQ (+ 2 FSETP/FSEL in cutoff mode) + 3 FMUL2 + 3 FFMA2.
-template <int R, int CUT>
+// UNI (all bodies have the same mass): the mu_j factor is hoisted out of the sum, 2 FMUL2 instead of 3;
+// the caller multiplies the finished sums by mu.  Padding bodies sit at 1e18, where rinv^3 underflows to 0.
+template <int R, int CUT, bool UNI, int UNROLL>
 __device__ __forceinline__ void tile_packed(const float4* __restrict__ T, const float2 (&nxi)[R],
                                             const float2 (&nyi)[R], const float2 (&nzi)[R], float2 eps2,
                                             float cut2, Acc<R>& out) {
     float2 ax[R], ay[R], az[R];
 #pragma unroll
     for (int b = 0; b < R; ++b) ax[b] = ay[b] = az[b] = make_float2(0.f, 0.f);
-#pragma unroll 2
+#pragma unroll UNROLL
     for (int jp = 0; jp < kJTile / 2; ++jp) {
         const float4 A = T[2 * jp], B = T[2 * jp + 1];
         const float2 xj = make_float2(A.x, A.y), yj = make_float2(A.z, A.w);
@@ -136,8 +138,13 @@ __device__ __forceinline__ void tile_packed(const float4* __restrict__ T, const 
                 ri.y = (r2.y >= cut2) ? ri.y : 0.f;
             }
             const float2 ri2 = __fmul2_rn(ri, ri);
-            float2 s = __fmul2_rn(mj, ri);      // (mu * rinv) * rinv^2: no overflow in SI units
-            s = __fmul2_rn(s, ri2);
+            float2 s;
+            if (UNI) {
+                s = __fmul2_rn(ri2, ri);
+            } else {
+                s = __fmul2_rn(mj, ri);          // (mu * rinv) * rinv^2: no overflow in SI units
+                s = __fmul2_rn(s, ri2);
+            }
             ax[b] = __ffma2_rn(s, dx, ax[b]);
             ay[b] = __ffma2_rn(s, dy, ay[b]);
             az[b] = __ffma2_rn(s, dz, az[b]);
@@ -194,9 +201,11 @@ __device__ __forceinline__ void tile_scalar(const float4* __restrict__ T, const 
 constexpr size_t kTileBytes = (size_t)kJTile * sizeof(float4);
 constexpr size_t kSmemBytes = kStages * kTileBytes + 2 * kStages * sizeof(uint64_t);
 
-template <int R, int CUT, bool PACKED>
-__global__ void __launch_bounds__(kThreads, (R <= 4) ? 2 : 1) force_step_kernel(const StepParams p) {
+// KIND: 0 scalar, 1 packed f32x2, 2 packed f32x2 with the uniform-mass hoist.
+template <int R, int THREADS, int MINB, int CUT, int KIND, int UNROLL>
+__global__ void __launch_bounds__(THREADS, MINB) force_step_kernel(const StepParams p) {
     static_assert(R % 2 == 0, "threads own whole i-pairs");
+    constexpr int kThreads = THREADS;     // shadows gs::kThreads: this variant's CTA size
     constexpr int ITILE = kThreads * R;
     constexpr int NP = R / 2;
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -273,8 +282,8 @@ __global__ void __launch_bounds__(kThreads, (R <= 4) ? 2 : 1) force_step_kernel(
             }
             mbar_wait(&full[stage], (uint32_t)((k / kStages) & 1));
             const float4* T = tiles + (size_t)stage * kJTile;
-            if (PACKED) tile_packed<R, CUT>(T, nxi, nyi, nzi, eps2, p.cut2, acc);
-            else tile_scalar<R, CUT>(T, nxi, nyi, nzi, eps2, p.cut2, acc);
+            if (KIND == 0) tile_scalar<R, CUT>(T, nxi, nyi, nzi, eps2, p.cut2, acc);
+            else tile_packed<R, CUT, KIND == 2, UNROLL>(T, nxi, nyi, nzi, eps2, p.cut2, acc);
             __syncwarp();
             if ((tid & 31) == 0) mbar_arrive(&empty[stage]);
         }
@@ -283,8 +292,9 @@ __global__ void __launch_bounds__(kThreads, (R <= 4) ? 2 : 1) force_step_kernel(
 #pragma unroll
         for (int q = 0; q < NP; ++q) {
             const int in_tile = 2 * (q * kThreads + tid);            // first body of the pair, in the tile
-            const float4 a0 = make_float4(acc.x[2 * q], acc.y[2 * q], acc.z[2 * q], 0.f);
-            const float4 a1 = make_float4(acc.x[2 * q + 1], acc.y[2 * q + 1], acc.z[2 * q + 1], 0.f);
+            const float w = (KIND == 2) ? p.mu_uniform : 1.f;        // hoisted mass factor
+            const float4 a0 = make_float4(w * acc.x[2 * q], w * acc.y[2 * q], w * acc.z[2 * q], 0.f);
+            const float4 a1 = make_float4(w * acc.x[2 * q + 1], w * acc.y[2 * q + 1], w * acc.z[2 * q + 1], 0.f);
             if (whole) {
                 finish_pair(p, (int)it * (ITILE / 2) + q * kThreads + tid, a0, a1);
             } else {
@@ -296,9 +306,7 @@ __global__ void __launch_bounds__(kThreads, (R <= 4) ? 2 : 1) force_step_kernel(
     }
 }
 
-template <int R>
-__global__ void __launch_bounds__(256) fixup_kernel(const StepParams p, int grid_main) {
-    constexpr int ITILE = kThreads * R;
+__global__ void __launch_bounds__(256) fixup_kernel(const StepParams p, int grid_main, int ITILE) {
     const int pair_local = blockIdx.x * blockDim.x + threadIdx.x;
     if (pair_local >= p.ni_tiles * (ITILE / 2)) return;
     const int64_t it = pair_local / (ITILE / 2);
@@ -321,40 +329,59 @@ __global__ void __launch_bounds__(256) fixup_kernel(const StepParams p, int grid
 // ------------------------------------------------------------------------------------------------
 // dispatch
 // ------------------------------------------------------------------------------------------------
-int variant_bodies_per_thread(int variant) {
+//            id  R  threads minB packed unroll
+#define GS_VARIANTS(X) \
+    X(1, 4, 256, 2, 1, 2)  \
+    X(2, 4, 256, 2, 0, 2)  \
+    X(3, 8, 256, 1, 1, 2)  \
+    X(4, 8, 256, 1, 0, 2)  \
+    X(5, 2, 256, 2, 1, 2)  \
+    X(6, 6, 256, 1, 1, 2)  \
+    X(7, 4, 512, 1, 1, 2)  \
+    X(8, 4, 256, 2, 1, 4)  \
+    X(9, 4, 256, 2, 1, 1)  \
+    X(10, 4, 128, 4, 1, 2) \
+    X(11, 6, 128, 3, 1, 2) \
+    X(12, 8, 128, 2, 1, 2) \
+    X(13, 2, 512, 2, 1, 2) \
+    X(14, 6, 256, 1, 1, 1) \
+    X(15, 8, 128, 2, 1, 1)
+
+bool variant_info(int variant, VariantInfo* out) {
     switch (variant) {
-        case 1: case 2: return 4;
-        case 3: case 4: return 8;
-        case 5: return 2;
-        case 6: return 6;
-        default: return 0;
+#define GS_X(ID, R_, T_, MB_, PK_, UN_) \
+    case ID: if (out) { out->R = R_; out->threads = T_; out->unroll = UN_; out->packed = PK_; out->i_tile = R_ * T_; } return true;
+        GS_VARIANTS(GS_X)
+#undef GS_X
+        default: return false;
     }
 }
 
 size_t force_smem_bytes() { return kSmemBytes; }
 
 typedef void (*ForceKernel)(const StepParams);
-static ForceKernel pick_force(int variant, int cut) {
-#define GS_PICK(R, PK) (cut == kCutoff ? (ForceKernel)force_step_kernel<R, kCutoff, PK> \
-                                       : (ForceKernel)force_step_kernel<R, kSoftened, PK>)
+static ForceKernel pick_force(int variant, int cut, bool uniform) {
     switch (variant) {
-        case 1: return GS_PICK(4, true);
-        case 2: return GS_PICK(4, false);
-        case 3: return GS_PICK(8, true);
-        case 4: return GS_PICK(8, false);
-        case 5: return GS_PICK(2, true);
-        case 6: return GS_PICK(6, true);
+#define GS_X(ID, R, T, MB, PK, UN)                                                                          \
+    case ID:                                                                                                \
+        if (PK && uniform)                                                                                  \
+            return cut == kCutoff ? (ForceKernel)force_step_kernel<R, T, MB, kCutoff, (PK ? 2 : 0), UN>     \
+                                  : (ForceKernel)force_step_kernel<R, T, MB, kSoftened, (PK ? 2 : 0), UN>;  \
+        return cut == kCutoff ? (ForceKernel)force_step_kernel<R, T, MB, kCutoff, PK, UN>                   \
+                              : (ForceKernel)force_step_kernel<R, T, MB, kSoftened, PK, UN>;
+        GS_VARIANTS(GS_X)
+#undef GS_X
         default: return nullptr;
     }
-#undef GS_PICK
 }
 
-cudaError_t force_kernel_occupancy(int variant, int cut_mode, int* ctas_per_sm, int* regs) {
-    ForceKernel k = pick_force(variant, cut_mode);
-    if (!k) return cudaErrorInvalidValue;
+cudaError_t force_kernel_occupancy(int variant, int cut_mode, bool uniform, int* ctas_per_sm, int* regs) {
+    ForceKernel k = pick_force(variant, cut_mode, uniform);
+    VariantInfo vi;
+    if (!k || !variant_info(variant, &vi)) return cudaErrorInvalidValue;
     cudaError_t e = cudaFuncSetAttribute((const void*)k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
     if (e != cudaSuccess) return e;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(ctas_per_sm, (const void*)k, kThreads, kSmemBytes);
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(ctas_per_sm, (const void*)k, vi.threads, kSmemBytes);
     if (e != cudaSuccess) return e;
     cudaFuncAttributes fa;
     e = cudaFuncGetAttributes(&fa, (const void*)k);
@@ -364,23 +391,20 @@ cudaError_t force_kernel_occupancy(int variant, int cut_mode, int* ctas_per_sm, 
 }
 
 cudaError_t launch_force(int variant, int cut_mode, const StepParams& p, int grid, cudaStream_t s) {
-    ForceKernel k = pick_force(variant, cut_mode);
-    if (!k) return cudaErrorInvalidValue;
-    k<<<grid, kThreads, kSmemBytes, s>>>(p);
+    const bool uniform = p.mu_uniform != 0.f;
+    ForceKernel k = pick_force(variant, cut_mode, uniform);
+    VariantInfo vi;
+    if (!k || !variant_info(variant, &vi)) return cudaErrorInvalidValue;
+    k<<<grid, vi.threads, kSmemBytes, s>>>(p);
     return cudaGetLastError();
 }
 
 cudaError_t launch_fixup(int variant, const StepParams& p, int grid_main, cudaStream_t s) {
-    const int R = variant_bodies_per_thread(variant);
-    const int pairs = p.ni_tiles * (kThreads * R / 2);
+    VariantInfo vi;
+    if (!variant_info(variant, &vi)) return cudaErrorInvalidValue;
+    const int pairs = p.ni_tiles * (vi.i_tile / 2);
     const int blocks = (pairs + 255) / 256;
-    switch (R) {
-        case 2: fixup_kernel<2><<<blocks, 256, 0, s>>>(p, grid_main); break;
-        case 4: fixup_kernel<4><<<blocks, 256, 0, s>>>(p, grid_main); break;
-        case 6: fixup_kernel<6><<<blocks, 256, 0, s>>>(p, grid_main); break;
-        case 8: fixup_kernel<8><<<blocks, 256, 0, s>>>(p, grid_main); break;
-        default: return cudaErrorInvalidValue;
-    }
+    fixup_kernel<<<blocks, 256, 0, s>>>(p, grid_main, vi.i_tile);
     return cudaGetLastError();
 }
 
@@ -403,8 +427,9 @@ __global__ void aos_to_packed_kernel(const T* __restrict__ aos, int n, int n_pad
             const double m = (double)r[6];
             mu[h] = (float)(G * m);          // never form m_i*m_j: G*m <= 1.33e20 fits fp32
             mass[i] = m;
-        } else {                             // padding: massless, at the origin, at rest
-            x[h] = y[h] = z[h] = vx[h] = vy[h] = vz[h] = mu[h] = 0.f;
+        } else {                             // padding: massless, at rest, so far away that rinv^3 underflows to 0
+            x[h] = y[h] = z[h] = kPadPosition;
+            vx[h] = vy[h] = vz[h] = mu[h] = 0.f;
             mass[i] = 0.0;
         }
     }

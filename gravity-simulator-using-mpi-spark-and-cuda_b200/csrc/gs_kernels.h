@@ -11,13 +11,13 @@ enum FinalMode : int { kFinalIntegrate = 0,   // v += a*kick_dt; x += v*drift_dt
                        kFinalKickOnly = 2 };  // v += a*kick_dt only (leapfrog velocity synchronisation)
 enum CutMode : int { kSoftened = 0, kCutoff = 1 };   // eps > 0  /  eps == 0 (reference r<1e-10 rule)
 
-// Kernel variants (gs_config.variant / env GRAVSIM_VARIANT). R = i-bodies per thread.
-//   1: R=4 packed f32x2 (default)   2: R=4 scalar   3: R=8 packed   4: R=8 scalar   5: R=2 packed
-//   6: R=6 packed
-constexpr int kNumVariants = 6;
+// Kernel variants (gs_config.variant / env GRAVSIM_VARIANT): i-bodies per thread R, CTA size, inner
+// unroll, packed f32x2 or scalar arithmetic.  The table lives in gs_kernels.cu (GS_VARIANTS).
+constexpr int kNumVariants = 15;
 constexpr int kDefaultVariant = 1;
-int variant_bodies_per_thread(int variant);           // 0 if the variant does not exist
-inline int variant_i_tile(int variant) { return kThreads * variant_bodies_per_thread(variant); }
+constexpr float kPadPosition = 1.0e18f;   // padding bodies: (1e18,1e18,1e18), mu = 0
+struct VariantInfo { int R, threads, unroll, packed, i_tile; };
+bool variant_info(int variant, VariantInfo* out);     // false if the variant does not exist
 
 struct StepParams {
     const float4* pos_old;   // packed pairs, n_pad bodies (all ranks' bodies)
@@ -36,12 +36,13 @@ struct StepParams {
     float cut2;              // kCutoff: pairs with r^2 < cut2 contribute nothing (1e-20)
     float kick_dt;           // v += a * kick_dt
     float drift_dt;          // x += v_new * drift_dt
+    float mu_uniform;        // != 0: every real body has this G*m; use the hoisted-mass kernel
     int final_mode;          // FinalMode
 };
 
 size_t force_smem_bytes();
 // Max resident CTAs per SM of the force kernel for this variant / cut mode, and its registers.
-cudaError_t force_kernel_occupancy(int variant, int cut_mode, int* ctas_per_sm, int* regs);
+cudaError_t force_kernel_occupancy(int variant, int cut_mode, bool uniform, int* ctas_per_sm, int* regs);
 cudaError_t launch_force(int variant, int cut_mode, const StepParams& p, int grid, cudaStream_t s);
 // Finishes the i-tiles whose units were split across CTAs (sums the partials, then integrates
 // or writes accelerations).  `grid_main` is the force kernel's grid.

@@ -68,6 +68,7 @@ typedef struct gs_config {
 
 #define GS_FLAG_NO_OVERLAP 1u   /* multi-GPU: gather first, then one force pass (debug/compare)  */
 #define GS_FLAG_TWO_PASS   2u   /* one GPU: run the multi-GPU local-then-remote two-pass schedule  */
+#define GS_FLAG_NO_UNIFORM_MASS 4u /* keep the general kernel even when all masses are equal        */
 
 typedef struct gs_info {
     int32_t n, n_pad;             /* bodies, padded bodies (multiple of the tile sizes)          */

@@ -105,13 +105,34 @@ def test_fp32_range_sun_and_heavy_body(gs, oracle):
     assert np.isfinite(a).all() and rel_err(a, oracle.accel(b.astype(np.float64))).max() <= ACC_TOL
 
 
-@pytest.mark.parametrize("variant", [1, 2, 3, 4, 5, 6])
+@pytest.mark.parametrize("variant", list(range(1, 16)))
 def test_every_kernel_variant(gs, oracle, variant):
     b = gs.ic_reference_uniform(3000, seed=variant)
     assert rel_err(gpu_accel(gs, b, variant=variant), oracle.accel(b.astype(np.float64))).max() <= ACC_TOL
     p = gs.ic_plummer(3000, seed=variant)
     ref = oracle.accel_subset(p.astype(np.float64), np.arange(3000), G=1.0, eps=0.05, massfree=True)[0]
-    assert rel_err(gpu_accel(gs, p, G=1.0, eps=0.05, variant=variant), ref).max() <= 5e-5
+    assert rel_err(gpu_accel(gs, p, G=1.0, eps=0.05, variant=variant), ref).max() <= 5e-5     # hoisted uniform mass
+    assert rel_err(gpu_accel(gs, p, G=1.0, eps=0.05, variant=variant, flags=gs.FLAG_NO_UNIFORM_MASS), ref).max() <= 5e-5
+
+
+def test_uniform_mass_path_equals_general_path(gs, oracle):
+    # equal masses select the kernel with the mass factor hoisted out of the inner loop; one different mass
+    # (or the flag) selects the general kernel.  Both must agree with the oracle, with padding (n not a tile multiple).
+    n = 5001
+    p = gs.ic_plummer(n, seed=3)
+    for eps, G in ((0.02, 1.0), (0.0, 1.0)):
+        ref = oracle.accel_subset(p.astype(np.float64), np.arange(n), G=G, eps=eps, massfree=True)[0]
+        a_uni = gpu_accel(gs, p, G=G, eps=eps)
+        a_gen = gpu_accel(gs, p, G=G, eps=eps, flags=gs.FLAG_NO_UNIFORM_MASS)
+        assert rel_err(a_uni, ref).max() <= 5e-5 and rel_err(a_gen, ref).max() <= 5e-5
+        assert rel_err(a_uni, a_gen.astype(np.float64)).max() <= 5e-6
+    ref = oracle.run_sync(p.astype(np.float64), 1.0 / 64, 5, G=1.0, eps=0.02)
+    for flags in (0, gs.FLAG_NO_UNIFORM_MASS, gs.FLAG_TWO_PASS):
+        with gs.GravSim(n, dt=1.0 / 64, G=1.0, eps=0.02, flags=flags) as sim:
+            sim.upload(p)
+            sim.step(5)
+            out = sim.download()
+        assert np.abs(out[:, :3] - ref[:, :3]).max() <= 1e-5 and np.abs(out[:, 3:6] - ref[:, 3:6]).max() <= 1e-5
 
 
 @pytest.mark.parametrize("grid", [1, 7, 100, 148])

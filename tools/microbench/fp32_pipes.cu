@@ -126,6 +126,32 @@ __global__ void __launch_bounds__(256) k_ffma_sel(float* out, float b, float c) 
     out[blockIdx.x * blockDim.x + threadIdx.x] = s;
 }
 
+
+// K independent FFMA2 + NM independent MUFU.RSQ per iteration: does a MUFU issue cost FMA-pipe cycles?
+template <int K, int NM>
+__global__ void __launch_bounds__(256) k_ffma2_mufu(float* out, float b, float c) {
+    float2 a[K];
+    float m[NM > 0 ? NM : 1];
+    float2 bb = make_float2(b, b * 1.0001f), cc = make_float2(c, c * 0.999f);
+#pragma unroll
+    for (int k = 0; k < K; ++k) a[k] = make_float2(threadIdx.x * 1e-3f + k, k * 0.5f);
+#pragma unroll
+    for (int k = 0; k < NM; ++k) m[k] = threadIdx.x * 1e-3f + k + 1.0f;
+    for (int it = 0; it < ITERS; ++it) {
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+            a[k] = __ffma2_rn(a[k], bb, cc);
+            if (k < NM) asm volatile("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(m[k]) : "f"(m[k]));
+        }
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < K; ++k) s += a[k].x + a[k].y;
+#pragma unroll
+    for (int k = 0; k < NM; ++k) s += m[k];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
 template <typename K>
 static void run(const char* name, K kern, int blocks_per_sm, double ops_per_thread_iter, int sms, float* d_out) {
     int grid = sms * blocks_per_sm;
@@ -154,7 +180,7 @@ int main() {
     int sms = p.multiProcessorCount;
     printf("device %s, %d SMs, clockRate %d kHz\n", p.name, sms, p.clockRate);
     float* d_out; CK(cudaMalloc(&d_out, (size_t)sms * 8 * 256 * sizeof(float)));
-    for (int bps : {4, 8}) {
+    for (int bps : {2, 4}) {
         run("ffma  (reg,const,const) ILP8", k_ffma<8>, bps, 8, sms, d_out);
         run("ffma3 (3 distinct regs) ILP8", k_ffma3<8>, bps, 8, sms, d_out);
         run("ffma2 packed ILP8 (x2 lanes)", k_ffma2<8>, bps, 16, sms, d_out);
@@ -164,6 +190,13 @@ int main() {
         run("mix rsq + 6 ffma ILP8", k_mix<8, 6>, bps, 8 * 7, sms, d_out);
         run("mix rsq + 12 ffma ILP8", k_mix<8, 12>, bps, 8 * 13, sms, d_out);
         run("ffma + setp/sel ILP8 (ffma only)", k_ffma_sel<8>, bps, 8, sms, d_out);
+        // lane-ops counted for the FFMA2 only (2 per lane): 128 = FMA pipe full
+        run("12 ffma2 + 0 mufu (ffma2 lanes)", k_ffma2_mufu<12, 0>, bps, 24, sms, d_out);
+        run("12 ffma2 + 1 mufu (ffma2 lanes)", k_ffma2_mufu<12, 1>, bps, 24, sms, d_out);
+        run("12 ffma2 + 2 mufu (ffma2 lanes)", k_ffma2_mufu<12, 2>, bps, 24, sms, d_out);
+        run("12 ffma2 + 3 mufu (ffma2 lanes)", k_ffma2_mufu<12, 3>, bps, 24, sms, d_out);
+        run("12 ffma2 + 4 mufu (ffma2 lanes)", k_ffma2_mufu<12, 4>, bps, 24, sms, d_out);
+        run("6 ffma2 + 1 mufu (ffma2 lanes)", k_ffma2_mufu<6, 1>, bps, 12, sms, d_out);
     }
     CK(cudaFree(d_out));
     return 0;

@@ -12,13 +12,13 @@ gs = load_package()
 PEAK = 148 * 128 * 2 * 1.965e9
 
 
-def probe(n, variant, eps, steps=4, grid=None):
+def probe(n, variant, eps, steps=4, grid=None, flags=0):
     b = gs.ic_plummer(n, seed=1) if eps > 0 else gs.ic_reference_uniform(n, seed=1)
     if grid:
         os.environ["GRAVSIM_GRID"] = str(grid)
     else:
         os.environ.pop("GRAVSIM_GRID", None)
-    with gs.GravSim(n, dt=1e-3 if eps > 0 else 3600.0, G=1.0 if eps > 0 else gs.G_SI, eps=eps, variant=variant) as sim:
+    with gs.GravSim(n, dt=1e-3 if eps > 0 else 3600.0, G=1.0 if eps > 0 else gs.G_SI, eps=eps, variant=variant, flags=flags) as sim:
         sim.upload(b)
         sim.step(2)
         sim.sync()
@@ -28,7 +28,7 @@ def probe(n, variant, eps, steps=4, grid=None):
         dt = (time.perf_counter() - t0) / steps
         info = sim.info
     rate = n * (n - 1.0) / dt
-    print(f"N={n:8d} variant={variant} mode={'soft' if eps > 0 else 'cut '} grid={info.grid} regs={info.regs_per_thread} "
+    print(f"N={n:8d} variant={variant:2d} thr={info.threads} itile={info.i_tile} mass={'general' if (flags & 4 or eps == 0) else 'uniform'} mode={'soft' if eps > 0 else 'cut '} grid={info.grid} regs={info.regs_per_thread} "
           f"{dt * 1e3:9.3f} ms/step  {rate:.3e} int/s  {rate * 20 / PEAK * 100:5.1f}% of 74.5 TF", flush=True)
 
 
@@ -37,5 +37,7 @@ if __name__ == "__main__":
     variants = [int(x) for x in sys.argv[2].split(",")] if len(sys.argv) > 2 else [1, 2, 3, 4, 5, 6]
     for n in ns:
         for v in variants:
-            for eps in (0.01, 0.0):
-                probe(n, v, eps)
+            probe(n, v, 0.01, flags=4)      # general masses, softened
+            probe(n, v, 0.01)               # equal masses (Plummer): hoisted-mass kernel
+            if len(sys.argv) > 3:
+                probe(n, v, 0.0)            # cutoff mode (reference-uniform SI bodies)
