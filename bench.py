@@ -286,7 +286,11 @@ def main():
                 "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True,
                 "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": dict(workload_config(world), n_bodies=n, variant=info.variant, grid=info.grid,
-                               i_tile=info.i_tile, j_tile=info.j_tile, regs=info.regs_per_thread),
+                               i_tile=info.i_tile, j_tile=info.j_tile, regs=info.regs_per_thread,
+                               mass_path="uniform (all masses equal: mass factor hoisted out of the inner loop)"
+                               if info.uniform_mass else "general",
+                               exchange=("peer-memory stores fused in the integrate epilogue + flags" if info.peer_exchange
+                                         else "ncclAllGather") if world > 1 else "none"),
                 "pct_fp32_peak": 100.0 * ach_tf / peak_tf,
                 "wall_ms_per_step_incl_l2_flush": t_wall / args.steps * 1e3,
                 "roofline": roof, "clocks": clocks,

@@ -20,6 +20,8 @@ G_SI = 6.67430e-11          # cuda.cu:11, mpi.c:9
 FLAG_NO_OVERLAP = 1
 FLAG_TWO_PASS = 2
 FLAG_NO_UNIFORM_MASS = 4
+FLAG_OVERLAP = 8
+FLAG_NCCL_EXCHANGE = 16
 NCCL_ID_BYTES = 128
 
 # every symbol include/gravsim.h declares (checked by the CPU tests)
@@ -60,7 +62,8 @@ class GsInfo(C.Structure):
         ("n", C.c_int32), ("n_pad", C.c_int32), ("i_begin", C.c_int32), ("i_end", C.c_int32),
         ("sm_count", C.c_int32), ("grid", C.c_int32), ("i_tile", C.c_int32), ("j_tile", C.c_int32),
         ("stages", C.c_int32), ("variant", C.c_int32), ("regs_per_thread", C.c_int32),
-        ("threads", C.c_int32), ("scratch_bytes", C.c_int64),
+        ("threads", C.c_int32), ("scratch_bytes", C.c_int64), ("peer_exchange", C.c_int32),
+        ("uniform_mass", C.c_int32),
     ]
 
 
@@ -300,10 +303,12 @@ class GravSim:
         else:
             r = _records(particles, np.float32)
             _check(lib().gs_upload_aos_f32(self._ctx, r.ctypes.data, r.shape[0]), "gs_upload_aos_f32", self._ctx)
+        lib().gs_get_info(self._ctx, C.byref(self.info))
 
     def upload_ptr(self, ptr, n, record_bytes=28):
         fn = lib().gs_upload_aos_f32 if record_bytes == 28 else lib().gs_upload_aos_f64
         _check(fn(self._ctx, C.c_void_p(ptr), n), "gs_upload_aos", self._ctx)
+        lib().gs_get_info(self._ctx, C.byref(self.info))
 
     def download(self, dtype=np.float32):
         out = np.empty((self.n, 7), dtype=dtype)

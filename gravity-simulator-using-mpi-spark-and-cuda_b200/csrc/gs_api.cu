@@ -5,6 +5,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <new>
+#include <unistd.h>
 
 #include "../../include/gravsim.h"
 #include "gs_kernels.h"
@@ -25,6 +26,7 @@ struct gs_ctx {
     float4* vel = nullptr;        // this rank's slice
     float4* vel_full = nullptr;   // world_size > 1: gathered velocities for download (lazy)
     float4* acc_local = nullptr;  // world_size > 1: accelerations from the local j-slice
+    float4* acc_stage = nullptr;  // peer-memory mode: accelerations handed from the force kernel to the finish kernel
     float4* acc_out = nullptr;    // gs_accel output (lazy)
     float4* partial = nullptr;    // split-tile scratch
     size_t partial_bytes = 0;
@@ -45,6 +47,17 @@ struct gs_ctx {
     int last_cuda_error = 0;
     int64_t steps_done = 0;
     bool split_full = false, split_local = false, split_remote = false;   // does a pass need the fix-up kernel
+    // peer-memory exchange (world_size > 1, all peers mappable): see setup_peer_exchange()
+    bool p2p = false;
+    float4* peer_pos[2][kMaxPeers + 1] = {};   // [buffer][rank]: every rank's pos buffers as seen from this GPU
+    uint32_t* flags = nullptr;                 // my flag array: flags[q] = exchanges rank q has completed into my buffers
+    uint32_t* peer_flags[kMaxPeers + 1] = {};  // rank q's flag array as seen from this GPU
+    void* ipc_opened[3 * (kMaxPeers + 1)] = {};
+    int n_ipc_opened = 0;
+    uint32_t* d_comm_err = nullptr;            // set by the wait kernel on timeout
+    uint32_t xstep = 0;                        // exchanges issued so far (same on every rank)
+    bool wait_pending = false;                 // pos[cur] still needs the peers' flags before remote bodies are read
+    unsigned long long comm_timeout_ns = 20000000000ull;
 };
 
 namespace {
@@ -74,6 +87,22 @@ int ensure_aos(gs_ctx* c, size_t bytes) {
     return GS_OK;
 }
 
+// Orders "every rank's bodies of pos[cur] are in this GPU's memory" before whatever is enqueued next on
+// the engine's stream.
+int wait_positions(gs_ctx* c) {
+    if (c->cfg.world_size <= 1) return GS_OK;
+    if (c->p2p) {
+        if (!c->wait_pending) return GS_OK;
+        GS_CUDA(c, launch_wait_flags(c->flags, c->cfg.world_size, c->cfg.rank, c->xstep, c->comm_timeout_ns,
+                                     c->d_comm_err, c->stream));
+        c->launches++;
+        c->wait_pending = false;
+        return GS_OK;
+    }
+    GS_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_gather[c->cur], 0));
+    return GS_OK;
+}
+
 // One force pass over this rank's i-bodies on the snapshot pos[cur].
 // world_size > 1 and overlap enabled: local j-slice first (needs nothing from the network), then
 // the remote slices once the all-gather of pos[cur] has landed.
@@ -94,43 +123,65 @@ int force_pass(gs_ctx* c, int final_mode, float kick, float drift, float4* acc_o
     p.drift_dt = drift;
     p.mu_uniform = c->mu_uniform;
     const int W = c->cfg.world_size;
-    // two passes: multi-GPU overlap, or GS_FLAG_TWO_PASS (same code path on one GPU, for tests)
-    const bool two_pass = ((W > 1) && !(c->cfg.flags & GS_FLAG_NO_OVERLAP)) ||
+    PeerTargets peers;
+    peers.n = 0;
+    if (c->p2p && final_mode == kFinalIntegrate) {   // fused exchange: the finish kernel stores into every peer's pos[nxt]
+        for (int q = 0; q < W; ++q)
+            if (q != c->cfg.rank) peers.pos_new[peers.n++] = c->peer_pos[c->cur ^ 1][q];
+    }
+    // two passes (own j-slice first, the rest once the peers' bodies are in): GS_FLAG_OVERLAP on several
+    // GPUs, or GS_FLAG_TWO_PASS (same code path on one GPU, for tests)
+    const bool two_pass = ((W > 1) && (c->cfg.flags & GS_FLAG_OVERLAP) && !(c->cfg.flags & GS_FLAG_NO_OVERLAP)) ||
                           ((W == 1) && (c->cfg.flags & GS_FLAG_TWO_PASS) && p.nj_total >= 2);
-    if (!two_pass) {
-        if (W > 1) GS_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_gather[c->cur], 0));
-        p.nj_tiles = p.nj_total; p.j_rot = 0;
-        p.acc_in = nullptr; p.acc_out = acc_out; p.final_mode = final_mode;
-        GS_CUDA(c, launch_force(c->variant, c->cut_mode, p, c->grid, c->stream)); c->launches++;
-        if (c->split_full) {
-            GS_CUDA(c, launch_fixup(c->variant, p, c->grid, c->stream)); c->launches++;
+    int rc;
+    // On several GPUs with the peer-memory exchange the integrating pass is finished by the finish kernel
+    // for EVERY tile (integration + stores into all peers' buffers in one kernel): the force kernel then
+    // only leaves accelerations in acc_stage.
+    auto run = [&](StepParams q, bool need_fixup) -> int {
+        const bool defer = c->p2p && q.final_mode == kFinalIntegrate;
+        StepParams f = q;
+        if (defer) { f.final_mode = kFinalAccOut; f.acc_out = c->acc_stage; }
+        GS_CUDA(c, launch_force(c->variant, c->cut_mode, f, c->grid, c->stream)); c->launches++;
+        if (need_fixup || defer) {
+            GS_CUDA(c, launch_fixup(c->variant, q, c->grid, defer ? c->acc_stage : nullptr, defer ? &peers : nullptr,
+                                    c->stream));
+            c->launches++;
         }
         return GS_OK;
+    };
+    if (!two_pass) {
+        if ((rc = wait_positions(c)) != GS_OK) return rc;
+        p.nj_tiles = p.nj_total; p.j_rot = 0;
+        p.acc_in = nullptr; p.acc_out = acc_out; p.final_mode = final_mode;
+        return run(p, c->split_full);
     }
     const int nj_local = (W > 1) ? c->slice / kJTile : p.nj_total / 2;
     const int rot_local = (W > 1) ? c->cfg.rank * nj_local : p.nj_total / 4;
     // pass L: j-tiles of this rank's own slice
     p.nj_tiles = nj_local; p.j_rot = rot_local;
     p.acc_in = nullptr; p.acc_out = c->acc_local; p.final_mode = kFinalAccOut;
-    GS_CUDA(c, launch_force(c->variant, c->cut_mode, p, c->grid, c->stream)); c->launches++;
-    if (c->split_local) {
-        GS_CUDA(c, launch_fixup(c->variant, p, c->grid, c->stream)); c->launches++;
-    }
+    if ((rc = run(p, c->split_local)) != GS_OK) return rc;
     // pass R: everything else, after the exchange
-    if (W > 1) GS_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_gather[c->cur], 0));
+    if ((rc = wait_positions(c)) != GS_OK) return rc;
     p.nj_tiles = p.nj_total - nj_local; p.j_rot = (rot_local + nj_local) % p.nj_total;
     p.acc_in = c->acc_local; p.acc_out = acc_out; p.final_mode = final_mode;
-    GS_CUDA(c, launch_force(c->variant, c->cut_mode, p, c->grid, c->stream)); c->launches++;
-    if (c->split_remote) {
-        GS_CUDA(c, launch_fixup(c->variant, p, c->grid, c->stream)); c->launches++;
-    }
-    return GS_OK;
+    return run(p, c->split_remote);
 }
 
 // Position exchange after an integrating pass wrote this rank's slice of pos[nxt]
 // (replaces MPI_Allgatherv + MPI_Barrier, mpi.c:227-236; 16 B/body instead of 56).
+//  peer-memory mode: the data already went out from the kernel's epilogue; only raise my counter on every peer.
+//  NCCL mode (fallback): in-place ncclAllGather on the comm stream.
 int exchange_positions(gs_ctx* c, int nxt) {
     if (c->cfg.world_size <= 1) return GS_OK;
+    if (c->p2p) {
+        PeerFlags f;
+        for (int q = 0; q < c->cfg.world_size; ++q) f.slot[q] = c->peer_flags[q] + c->cfg.rank;
+        c->xstep++;
+        GS_CUDA(c, launch_signal_peers(f, c->cfg.world_size, c->cfg.rank, c->xstep, c->stream)); c->launches++;
+        c->wait_pending = true;
+        return GS_OK;
+    }
     NcclApi& nc = nccl_api();
     GS_CUDA(c, cudaEventRecord(c->ev_integ, c->stream));
     GS_CUDA(c, cudaStreamWaitEvent(c->comm_stream, c->ev_integ, 0));
@@ -155,13 +206,122 @@ int sync_velocities(gs_ctx* c) {
 // 78.7 % equal masses), cutoff -> R=8 x 256 threads (65.2 %).  R=6 has a 1536-body i-tile, which pads some
 // N / GPU-count combinations more than the 2048-body tile of R=8 does: charge each its padded work.
 int default_variant(int n, int world, int cut_mode) {
-    if (cut_mode == kCutoff) return 3;
     int pad6 = 0, pad3 = 0;
     if (gs_plan_slice(n, world, 0, 6, &pad6, nullptr, nullptr) != GS_OK ||
         gs_plan_slice(n, world, 0, 3, &pad3, nullptr, nullptr) != GS_OK)
         return kDefaultVariant;
+    // small problems: too few (i-tile x j-tile) units to feed 148 SMs -> 512-body i-tiles, 4 CTAs per SM
+    const int64_t units6 = ((int64_t)pad6 / world / 1536) * (pad6 / kJTile);
+    if (units6 < 8 * 148) return 10;
+    if (cut_mode == kCutoff) return 3;
     const double cost6 = (double)pad6 * pad6, cost3 = (double)pad3 * pad3 / 0.98;
     return cost6 <= cost3 ? 6 : 3;
+}
+
+// ---- peer-memory exchange set-up ----------------------------------------------------------------
+// Every rank publishes IPC handles (other processes) and raw pointers (other threads of this process)
+// of its two position buffers and its flag array; NCCL is only the courier here, once.  If any rank
+// cannot map any peer, all ranks stay on the NCCL all-gather path together.
+struct PeerBlob {
+    long long pid;
+    int device, ok;
+    cudaIpcMemHandle_t handle[3];
+    void* raw[3];
+    char pad[256 - 16 - 3 * sizeof(cudaIpcMemHandle_t) - 3 * sizeof(void*)];
+};
+static_assert(sizeof(PeerBlob) == 256, "PeerBlob is exchanged as 256 raw bytes");
+
+void close_peer_mappings(gs_ctx* c) {
+    for (int k = 0; k < c->n_ipc_opened; ++k) cudaIpcCloseMemHandle(c->ipc_opened[k]);
+    c->n_ipc_opened = 0;
+}
+
+int setup_peer_exchange(gs_ctx* c) {
+    const int W = c->cfg.world_size, me = c->cfg.rank;
+    if (W > kMaxPeers + 1 || (c->cfg.flags & GS_FLAG_NCCL_EXCHANGE)) return GS_OK;
+    NcclApi& nc = nccl_api();
+    if (const char* t = getenv("GRAVSIM_COMM_TIMEOUT_S")) c->comm_timeout_ns = (unsigned long long)(atof(t) * 1e9);
+    GS_CUDA(c, cudaMalloc((void**)&c->flags, 64 * sizeof(uint32_t)));
+    GS_CUDA(c, cudaMalloc((void**)&c->d_comm_err, sizeof(uint32_t)));
+    GS_CUDA(c, cudaMemsetAsync(c->flags, 0, 64 * sizeof(uint32_t), c->stream));
+    GS_CUDA(c, cudaMemsetAsync(c->d_comm_err, 0, sizeof(uint32_t), c->stream));
+    PeerBlob mine;
+    memset(&mine, 0, sizeof(mine));
+    mine.pid = (long long)getpid();
+    mine.device = c->device;
+    mine.ok = 1;
+    void* ptrs[3] = {c->pos[0], c->pos[1], c->flags};
+    for (int k = 0; k < 3; ++k) {
+        mine.raw[k] = ptrs[k];
+        if (cudaIpcGetMemHandle(&mine.handle[k], ptrs[k]) != cudaSuccess) { cudaGetLastError(); mine.ok = 0; }
+    }
+    PeerBlob* d_blobs = nullptr;
+    PeerBlob* h_blobs = new (std::nothrow) PeerBlob[W];
+    if (!h_blobs) return GS_ENOMEM;
+    int* d_ok = nullptr;
+    int rc = GS_OK, all_ok = 0;
+    do {
+        if (cudaMalloc((void**)&d_blobs, sizeof(PeerBlob) * W) != cudaSuccess ||
+            cudaMalloc((void**)&d_ok, sizeof(int)) != cudaSuccess) { rc = GS_ENOMEM; break; }
+        if (cudaMemcpyAsync(d_blobs + me, &mine, sizeof(mine), cudaMemcpyHostToDevice, c->stream) != cudaSuccess ||
+            nc.AllGather(d_blobs + me, d_blobs, sizeof(PeerBlob), ncclChar, c->comm, c->stream) != ncclSuccess ||
+            cudaMemcpyAsync(h_blobs, d_blobs, sizeof(PeerBlob) * W, cudaMemcpyDeviceToHost, c->stream) != cudaSuccess ||
+            cudaStreamSynchronize(c->stream) != cudaSuccess) { rc = GS_ENCCL; break; }
+        int ok = 1;
+        for (int q = 0; q < W && ok; ++q) ok = h_blobs[q].ok;
+        for (int q = 0; q < W && ok; ++q) {
+            if (q == me) {
+                c->peer_pos[0][q] = c->pos[0]; c->peer_pos[1][q] = c->pos[1]; c->peer_flags[q] = c->flags;
+                continue;
+            }
+            void* mapped[3] = {nullptr, nullptr, nullptr};
+            if (h_blobs[q].pid == mine.pid) {        // another thread of this process: plain peer access
+                int can = 0;
+                if (cudaDeviceCanAccessPeer(&can, c->device, h_blobs[q].device) != cudaSuccess || !can) { ok = 0; break; }
+                cudaError_t e = cudaDeviceEnablePeerAccess(h_blobs[q].device, 0);
+                if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) { ok = 0; break; }
+                cudaGetLastError();
+                for (int k = 0; k < 3; ++k) mapped[k] = h_blobs[q].raw[k];
+            } else {                                 // another process: CUDA IPC
+                for (int k = 0; k < 3 && ok; ++k) {
+                    if (cudaIpcOpenMemHandle(&mapped[k], h_blobs[q].handle[k], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+                        cudaGetLastError(); ok = 0;
+                    } else {
+                        c->ipc_opened[c->n_ipc_opened++] = mapped[k];
+                    }
+                }
+                if (!ok) break;
+            }
+            c->peer_pos[0][q] = (float4*)mapped[0]; c->peer_pos[1][q] = (float4*)mapped[1];
+            c->peer_flags[q] = (uint32_t*)mapped[2];
+        }
+        // unanimous decision
+        if (cudaMemcpyAsync(d_ok, &ok, sizeof(int), cudaMemcpyHostToDevice, c->stream) != cudaSuccess ||
+            nc.AllReduce(d_ok, d_ok, 1, ncclInt, ncclMin, c->comm, c->stream) != ncclSuccess ||
+            cudaMemcpyAsync(&all_ok, d_ok, sizeof(int), cudaMemcpyDeviceToHost, c->stream) != cudaSuccess ||
+            cudaStreamSynchronize(c->stream) != cudaSuccess) { rc = GS_ENCCL; break; }
+    } while (0);
+    cudaFree(d_blobs); cudaFree(d_ok);
+    delete[] h_blobs;
+    if (rc != GS_OK) return rc;
+    if (all_ok) {
+        GS_CUDA(c, cudaMalloc((void**)&c->acc_stage, (size_t)c->slice * sizeof(float4)));
+        c->p2p = true;
+    } else {
+        close_peer_mappings(c);
+    }
+    return GS_OK;
+}
+
+// Collective farewell in peer-memory mode: nobody unmaps or frees while a peer may still store into it.
+void peer_exchange_goodbye(gs_ctx* c) {
+    if (!c->p2p) return;
+    PeerFlags f;
+    for (int q = 0; q < c->cfg.world_size; ++q) f.slot[q] = c->peer_flags[q] + c->cfg.rank;
+    c->xstep++;
+    launch_signal_peers(f, c->cfg.world_size, c->cfg.rank, c->xstep, c->stream);
+    launch_wait_flags(c->flags, c->cfg.world_size, c->cfg.rank, c->xstep, 5000000000ull, c->d_comm_err, c->stream);
+    cudaStreamSynchronize(c->stream);
 }
 
 int set_device(gs_ctx* c) {
@@ -181,7 +341,7 @@ const char* gs_strerror(int code) {
         case GS_EINVAL: return "invalid argument";
         case GS_ECUDA: return "CUDA runtime error (see gs_last_cuda_error)";
         case GS_ENOMEM: return "out of memory";
-        case GS_ENCCL: return "NCCL unavailable or collective failed";
+        case GS_ENCCL: return "NCCL unavailable, collective failed or peer exchange timed out";
         case GS_ESTATE: return "call out of order";
         case GS_ENOGPU: return "no CUDA device available (libgravsim has no CPU path)";
         case GS_EIO: return "state-file I/O error";
@@ -269,11 +429,14 @@ int gs_host_free(void* ptr) { return cudaFreeHost(ptr) == cudaSuccess ? GS_OK : 
 void gs_destroy(gs_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
+    peer_exchange_goodbye(c);
     if (c->stream) cudaStreamSynchronize(c->stream);
     if (c->comm_stream) cudaStreamSynchronize(c->comm_stream);
+    close_peer_mappings(c);
+    cudaFree(c->flags); cudaFree(c->d_comm_err);
     if (c->comm) nccl_api().CommDestroy(c->comm);
     cudaFree(c->pos[0]); cudaFree(c->pos[1]); cudaFree(c->vel); cudaFree(c->vel_full);
-    cudaFree(c->acc_local); cudaFree(c->acc_out); cudaFree(c->partial); cudaFree(c->mass);
+    cudaFree(c->acc_local); cudaFree(c->acc_stage); cudaFree(c->acc_out); cudaFree(c->partial); cudaFree(c->mass);
     cudaFree(c->d_aos); cudaFree(c->d_energy);
     if (c->h_energy) cudaFreeHost(c->h_energy);
     if (c->h_acc) cudaFreeHost(c->h_acc);
@@ -301,6 +464,7 @@ int gs_create(gs_ctx** out, const gs_config* cfg) {
     if (!c) return GS_ENOMEM;
     c->cfg = *cfg;
     c->cfg.nccl_id = nullptr;
+    if (const char* ef = getenv("GRAVSIM_FLAGS")) c->cfg.flags |= (uint32_t)atoi(ef);   // experiments
     int rc = GS_OK;
     auto fail = [&](int code) { gs_destroy(c); return code; };
 
@@ -351,7 +515,7 @@ int gs_create(gs_ctx** out, const gs_config* cfg) {
         if (cfg->world_size > 1) {
             c->split_local = any_split(ni, njl, c->grid);
             c->split_remote = any_split(ni, nj - njl, c->grid);
-        } else if ((cfg->flags & GS_FLAG_TWO_PASS) && nj >= 2) {
+        } else if ((c->cfg.flags & GS_FLAG_TWO_PASS) && nj >= 2) {
             c->split_local = any_split(ni, nj / 2, c->grid);
             c->split_remote = any_split(ni, nj - nj / 2, c->grid);
         }
@@ -367,7 +531,7 @@ int gs_create(gs_ctx** out, const gs_config* cfg) {
         !dmalloc((void**)&c->mass, (size_t)c->n_pad * sizeof(double)) ||
         !dmalloc((void**)&c->d_energy, ((size_t)egrid * 5 + 8) * sizeof(double)))
         return fail(GS_ENOMEM);
-    if ((cfg->world_size > 1 || (cfg->flags & GS_FLAG_TWO_PASS)) && !dmalloc((void**)&c->acc_local, vel_bytes))
+    if ((cfg->world_size > 1 || (c->cfg.flags & GS_FLAG_TWO_PASS)) && !dmalloc((void**)&c->acc_local, vel_bytes))
         return fail(GS_ENOMEM);
     if (cudaHostAlloc((void**)&c->h_energy, ((size_t)egrid * 5 + 8) * sizeof(double), cudaHostAllocDefault) !=
         cudaSuccess)
@@ -389,6 +553,7 @@ int gs_create(gs_ctx** out, const gs_config* cfg) {
         ncclUniqueId id;
         memcpy(&id, cfg->nccl_id, sizeof(id));
         if (nc.CommInitRank(&c->comm, cfg->world_size, id, cfg->rank) != ncclSuccess) return fail(GS_ENCCL);
+        if ((rc = setup_peer_exchange(c)) != GS_OK) return fail(rc);
     }
     *out = c;
     return GS_OK;
@@ -431,10 +596,16 @@ static int upload_common(gs_ctx* c, const void* host, int n, int record_bytes) {
     GS_CUDA(c, cudaMemcpyAsync(c->pos[1], c->pos[0], (size_t)c->n_pad * sizeof(float4), cudaMemcpyDeviceToDevice,
                                c->stream));
     if (c->cfg.world_size > 1) {
-        // every rank uploaded the full array: pos[0] is already "gathered"
-        GS_CUDA(c, cudaEventRecord(c->ev_integ, c->stream));
-        GS_CUDA(c, cudaStreamWaitEvent(c->comm_stream, c->ev_integ, 0));
-        GS_CUDA(c, cudaEventRecord(c->ev_gather[0], c->comm_stream));
+        // every rank uploaded the full array: pos[0] is already complete everywhere.
+        if (c->p2p) {
+            // still an exchange epoch: no peer may start storing the next step into my buffers before I am
+            // done with the old contents (my stream has passed this point), and vice versa.
+            if ((rc = exchange_positions(c, 0)) != GS_OK) return rc;
+        } else {
+            GS_CUDA(c, cudaEventRecord(c->ev_integ, c->stream));
+            GS_CUDA(c, cudaStreamWaitEvent(c->comm_stream, c->ev_integ, 0));
+            GS_CUDA(c, cudaEventRecord(c->ev_gather[0], c->comm_stream));
+        }
     }
     c->uploaded = true;
     c->vel_synced = true;
@@ -463,7 +634,7 @@ int gs_step(gs_ctx* c, int nsteps) {
     }
     // order the last exchange on the caller-visible stream too, so an event recorded there after
     // gs_step covers every byte of the step (positions are then valid on every rank)
-    if (c->cfg.world_size > 1 && nsteps > 0) GS_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_gather[c->cur], 0));
+    if (c->cfg.world_size > 1 && nsteps > 0 && (rc = wait_positions(c)) != GS_OK) return rc;
     return GS_OK;
 }
 
@@ -501,7 +672,7 @@ int gs_energy(gs_ctx* c, double* kinetic, double* potential, double momentum[3])
     int rc = set_device(c);
     if (rc != GS_OK) return rc;
     if ((rc = sync_velocities(c)) != GS_OK) return rc;
-    if (c->cfg.world_size > 1) GS_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_gather[c->cur], 0));
+    if ((rc = wait_positions(c)) != GS_OK) return rc;
     const int egrid = energy_grid(c->slice);
     double* d_pot = c->d_energy;
     double* d_kin = c->d_energy + egrid;
@@ -545,7 +716,7 @@ static int download_common(gs_ctx* c, void* host, int n, int record_bytes) {
     if (c->cfg.world_size > 1) {
         NcclApi& nc = nccl_api();
         if (!c->vel_full) GS_CUDA(c, cudaMalloc((void**)&c->vel_full, (size_t)c->n_pad * sizeof(float4)));
-        GS_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_gather[c->cur], 0));
+        if ((rc = wait_positions(c)) != GS_OK) return rc;
         if (nc.AllGather(c->vel, c->vel_full, (size_t)c->slice * 4, ncclFloat, c->comm, c->stream) != ncclSuccess)
             return GS_ENCCL;
         vel_full = c->vel_full;
@@ -568,6 +739,11 @@ int gs_sync(gs_ctx* c) {
     if (rc != GS_OK) return rc;
     GS_CUDA(c, cudaStreamSynchronize(c->stream));
     if (c->comm_stream) GS_CUDA(c, cudaStreamSynchronize(c->comm_stream));
+    if (c->p2p) {      // a peer never raised its flag: the wait kernel gave up instead of hanging the GPU
+        uint32_t err = 0;
+        GS_CUDA(c, cudaMemcpy(&err, c->d_comm_err, sizeof(err), cudaMemcpyDeviceToHost));
+        if (err) return GS_ENCCL;
+    }
     return GS_OK;
 }
 
@@ -594,6 +770,8 @@ int gs_get_info(const gs_ctx* c, gs_info* info) {
     info->stages = kStages; info->variant = c->variant;
     info->regs_per_thread = c->regs; info->threads = c->threads;
     info->scratch_bytes = (int64_t)c->partial_bytes;
+    info->peer_exchange = c->p2p ? 1 : 0;
+    info->uniform_mass = c->mu_uniform != 0.f ? 1 : 0;
     return GS_OK;
 }
 

@@ -71,7 +71,13 @@ __device__ __forceinline__ float rsqrt_approx(float x) {
 // finishing one i-pair: add upstream accelerations, then write them out or integrate
 //   v += a * kick_dt ; x += v_new * drift_dt          (cuda.cu:73-76, mpi.c:207-215)
 // ------------------------------------------------------------------------------------------------
-__device__ __forceinline__ void finish_pair(const StepParams& p, int pair_local, float4 a0, float4 a1) {
+// PEERS: also store the new positions into every peer GPU's buffer (the exchange, fused with the
+// integration).  Only the finishing kernel is built with PEERS = true: compiled into the force kernel the
+// extra loop perturbs ptxas' schedule of the hot inner loop (measured -2.5 %), so on several GPUs the
+// force kernel hands its accelerations to finish_kernel instead (16 B per body, negligible).
+template <bool PEERS>
+__device__ __forceinline__ void finish_pair(const StepParams& p, int pair_local, float4 a0, float4 a1,
+                                            const PeerTargets* peers = nullptr) {
     if (p.acc_in != nullptr) {
         const float4 b0 = p.acc_in[2 * pair_local], b1 = p.acc_in[2 * pair_local + 1];
         a0.x += b0.x; a0.y += b0.y; a0.z += b0.z;
@@ -98,6 +104,14 @@ __device__ __forceinline__ void finish_pair(const StepParams& p, int pair_local,
     PA.z = fmaf(VA.z, p.drift_dt, PA.z); PA.w = fmaf(VA.w, p.drift_dt, PA.w);
     PB.x = fmaf(VB.x, p.drift_dt, PB.x); PB.y = fmaf(VB.y, p.drift_dt, PB.y);
     p.pos_new[2 * pair_global] = PA; p.pos_new[2 * pair_global + 1] = PB;   // PB.zw = mu, unchanged
+    if (PEERS) {
+        // same 32 B to every peer over NVLink (replaces MPI_Allgatherv, mpi.c:227-231); made visible to the
+        // peers by the flag protocol of signal_peers_kernel / wait_flags_kernel
+        for (int q = 0; q < peers->n; ++q) {
+            float4* dst = peers->pos_new[q] + 2 * (size_t)pair_global;
+            dst[0] = PA; dst[1] = PB;
+        }
+    }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -296,7 +310,7 @@ __global__ void __launch_bounds__(THREADS, MINB) force_step_kernel(const StepPar
             const float4 a0 = make_float4(w * acc.x[2 * q], w * acc.y[2 * q], w * acc.z[2 * q], 0.f);
             const float4 a1 = make_float4(w * acc.x[2 * q + 1], w * acc.y[2 * q + 1], w * acc.z[2 * q + 1], 0.f);
             if (whole) {
-                finish_pair(p, (int)it * (ITILE / 2) + q * kThreads + tid, a0, a1);
+                finish_pair<false>(p, (int)it * (ITILE / 2) + q * kThreads + tid, a0, a1);
             } else {
                 const int slot = (it == first_tile) ? 0 : 1;
                 float4* dst = p.partial + ((size_t)blockIdx.x * 2 + slot) * ITILE + in_tile;
@@ -306,13 +320,25 @@ __global__ void __launch_bounds__(THREADS, MINB) force_step_kernel(const StepPar
     }
 }
 
-__global__ void __launch_bounds__(256) fixup_kernel(const StepParams p, int grid_main, int ITILE) {
+// Finishes i-tiles after the force kernel:
+//   split tiles   : sums the per-CTA partials in fixed CTA order, then finish_pair;
+//   whole tiles   : untouched (already finished in the force kernel), unless `whole_acc` is given --
+//                   then the force kernel only stored their accelerations there and this kernel finishes
+//                   them too (multi-GPU: integration + peer stores happen here, for every body).
+__global__ void __launch_bounds__(256) fixup_kernel(const StepParams p, int grid_main, int ITILE,
+                                                    const float4* __restrict__ whole_acc, const PeerTargets peers) {
     const int pair_local = blockIdx.x * blockDim.x + threadIdx.x;
     if (pair_local >= p.ni_tiles * (ITILE / 2)) return;
     const int64_t it = pair_local / (ITILE / 2);
     const int q = pair_local - (int)it * (ITILE / 2);
     const TileOwners o = tile_owners(p.ni_tiles, p.nj_tiles, grid_main, it);
-    if (!o.split) return;   // finished inside the force kernel
+    if (!o.split) {
+        if (whole_acc == nullptr) return;   // finished inside the force kernel
+        StepParams pw = p;
+        pw.acc_in = nullptr;                // the force kernel already added the upstream accelerations
+        finish_pair<true>(pw, pair_local, whole_acc[2 * pair_local], whole_acc[2 * pair_local + 1], &peers);
+        return;
+    }
     const int64_t U = (int64_t)p.ni_tiles * p.nj_tiles;
     float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0;
     for (int c = o.first; c <= o.last; ++c) {   // fixed order: bit-reproducible
@@ -323,7 +349,7 @@ __global__ void __launch_bounds__(256) fixup_kernel(const StepParams p, int grid
         a0.x += s0.x; a0.y += s0.y; a0.z += s0.z;
         a1.x += s1.x; a1.y += s1.y; a1.z += s1.z;
     }
-    finish_pair(p, pair_local, a0, a1);
+    finish_pair<true>(p, pair_local, a0, a1, &peers);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -399,12 +425,53 @@ cudaError_t launch_force(int variant, int cut_mode, const StepParams& p, int gri
     return cudaGetLastError();
 }
 
-cudaError_t launch_fixup(int variant, const StepParams& p, int grid_main, cudaStream_t s) {
+cudaError_t launch_fixup(int variant, const StepParams& p, int grid_main, const float4* whole_acc,
+                         const PeerTargets* peers, cudaStream_t s) {
     VariantInfo vi;
     if (!variant_info(variant, &vi)) return cudaErrorInvalidValue;
     const int pairs = p.ni_tiles * (vi.i_tile / 2);
     const int blocks = (pairs + 255) / 256;
-    fixup_kernel<<<blocks, 256, 0, s>>>(p, grid_main, vi.i_tile);
+    PeerTargets none;
+    none.n = 0;
+    fixup_kernel<<<blocks, 256, 0, s>>>(p, grid_main, vi.i_tile, whole_acc, peers ? *peers : none);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------------
+// peer-memory exchange: flags
+// ------------------------------------------------------------------------------------------------
+__global__ void signal_peers_kernel(PeerFlags f, int world, int my_rank, uint32_t value) {
+    const int q = threadIdx.x;
+    if (q < world && q != my_rank) {
+        __threadfence_system();                                  // earlier kernels' peer stores are ordered before the flag
+        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(f.slot[q]), "r"(value) : "memory");
+    }
+}
+
+__global__ void wait_flags_kernel(const uint32_t* my_flags, int world, int my_rank, uint32_t value,
+                                  unsigned long long timeout_ns, uint32_t* err) {
+    const int q = threadIdx.x;
+    if (q >= world || q == my_rank) return;
+    unsigned long long t0;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    for (;;) {
+        uint32_t v;
+        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(my_flags + q) : "memory");
+        if ((int32_t)(v - value) >= 0) break;                    // counters only grow (wrap-safe compare)
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        if (t - t0 > timeout_ns) { *err = 1u; break; }           // never hang the GPU on a lost peer
+        __nanosleep(200);
+    }
+}
+
+cudaError_t launch_signal_peers(const PeerFlags& f, int world, int my_rank, uint32_t value, cudaStream_t s) {
+    signal_peers_kernel<<<1, 32, 0, s>>>(f, world, my_rank, value);
+    return cudaGetLastError();
+}
+cudaError_t launch_wait_flags(const uint32_t* my_flags, int world, int my_rank, uint32_t value,
+                              unsigned long long timeout_ns, uint32_t* err, cudaStream_t s) {
+    wait_flags_kernel<<<1, 32, 0, s>>>(my_flags, world, my_rank, value, timeout_ns, err);
     return cudaGetLastError();
 }
 

@@ -19,6 +19,8 @@ constexpr float kPadPosition = 1.0e18f;   // padding bodies: (1e18,1e18,1e18), m
 struct VariantInfo { int R, threads, unroll, packed, i_tile; };
 bool variant_info(int variant, VariantInfo* out);     // false if the variant does not exist
 
+constexpr int kMaxPeers = 7;   // direct peer-memory exchange supports up to 8 GPUs (one NVSwitch domain)
+
 struct StepParams {
     const float4* pos_old;   // packed pairs, n_pad bodies (all ranks' bodies)
     float4* pos_new;         // packed pairs, n_pad bodies; only this rank's slice is written
@@ -40,13 +42,29 @@ struct StepParams {
     int final_mode;          // FinalMode
 };
 
+// Peers' pos_new buffers (NVLink peer memory, same indexing as StepParams::pos_new).  Kept out of StepParams:
+// growing the force kernel's parameter block changes ptxas' schedule of its inner loop (measured -2.5 %).
+struct PeerTargets { int n; float4* pos_new[kMaxPeers]; };
+
 size_t force_smem_bytes();
 // Max resident CTAs per SM of the force kernel for this variant / cut mode, and its registers.
 cudaError_t force_kernel_occupancy(int variant, int cut_mode, bool uniform, int* ctas_per_sm, int* regs);
 cudaError_t launch_force(int variant, int cut_mode, const StepParams& p, int grid, cudaStream_t s);
 // Finishes the i-tiles whose units were split across CTAs (sums the partials, then integrates
 // or writes accelerations).  `grid_main` is the force kernel's grid.
-cudaError_t launch_fixup(int variant, const StepParams& p, int grid_main, cudaStream_t s);
+// whole_acc != nullptr: also finish the whole tiles, whose accelerations the force kernel left there.
+cudaError_t launch_fixup(int variant, const StepParams& p, int grid_main, const float4* whole_acc,
+                         const PeerTargets* peers, cudaStream_t s);
+
+// Peer-memory exchange (replaces the per-step collective when every GPU can map its peers' buffers):
+// the integrating epilogue stores new positions straight into every peer's position buffer over
+// NVLink; afterwards each rank raises a step counter in every peer's flag array, and before a pass
+// that reads remote bodies it waits until all peers' counters have reached the step it needs.
+struct PeerFlags { uint32_t* slot[kMaxPeers + 1]; };   // slot[q] = address of "my" counter inside rank q's flag array
+cudaError_t launch_signal_peers(const PeerFlags& f, int world, int my_rank, uint32_t value, cudaStream_t s);
+// Spins (bounded by timeout_ns) until flags[q] >= value for all q != my_rank; on timeout sets *err = 1.
+cudaError_t launch_wait_flags(const uint32_t* my_flags, int world, int my_rank, uint32_t value,
+                              unsigned long long timeout_ns, uint32_t* err, cudaStream_t s);
 
 // AoS <-> packed-pair conversion on the device. `aos` is the raw byte image of the reference's
 // 28-byte (f32) or 56-byte (f64) records.  Bodies >= n are padding (mu = 0, at the origin).

@@ -33,7 +33,7 @@ extern "C" {
 #define GS_EINVAL   -1   /* bad argument / config                                  */
 #define GS_ECUDA    -2   /* a CUDA runtime call failed; see gs_last_cuda_error()   */
 #define GS_ENOMEM   -3   /* host or device allocation failed                       */
-#define GS_ENCCL    -4   /* NCCL missing or a collective failed                    */
+#define GS_ENCCL    -4   /* NCCL missing, a collective failed, or a peer timed out */
 #define GS_ESTATE   -5   /* call out of order (e.g. step before upload)            */
 #define GS_ENOGPU   -6   /* no CUDA device: this library has no CPU path           */
 #define GS_EIO      -7   /* state-file I/O failed                                  */
@@ -66,9 +66,11 @@ typedef struct gs_config {
     int32_t  variant;       /* kernel variant; 0 = default (see gs_info.variant)                 */
 } gs_config;
 
-#define GS_FLAG_NO_OVERLAP 1u   /* multi-GPU: gather first, then one force pass (debug/compare)  */
+#define GS_FLAG_NO_OVERLAP 1u   /* (default behaviour; kept for callers that set it) one force pass per step    */
 #define GS_FLAG_TWO_PASS   2u   /* one GPU: run the multi-GPU local-then-remote two-pass schedule  */
 #define GS_FLAG_NO_UNIFORM_MASS 4u /* keep the general kernel even when all masses are equal        */
+#define GS_FLAG_OVERLAP    8u   /* multi-GPU: own j-slice first, remote slices after the exchange  */
+#define GS_FLAG_NCCL_EXCHANGE 16u /* multi-GPU: per-step ncclAllGather instead of peer-memory stores */
 
 typedef struct gs_info {
     int32_t n, n_pad;             /* bodies, padded bodies (multiple of the tile sizes)          */
@@ -79,6 +81,8 @@ typedef struct gs_info {
     int32_t regs_per_thread;      /* of the force kernel (cudaFuncGetAttributes)                 */
     int32_t threads;              /* threads per CTA                                             */
     int64_t scratch_bytes;        /* device scratch for split-tile partial sums                  */
+    int32_t peer_exchange;        /* 1: positions travel by peer-memory stores; 0: ncclAllGather  */
+    int32_t uniform_mass;         /* 1: hoisted-mass kernel in use (all masses equal)            */
 } gs_info;
 
 /* ---- life cycle -------------------------------------------------------------------------- */

@@ -297,7 +297,8 @@ def test_two_gpus_when_present(gs, oracle):
     n = 20000
     b = gs.ic_reference_uniform(n, seed=31)
     ref = oracle.run_sync(b.astype(np.float64), 3600.0, 6)
-    for flags in (0, gs.FLAG_NO_OVERLAP):
+    # peer-memory exchange (default), with the two-pass overlap schedule, and the NCCL all-gather fallback
+    for flags in (0, gs.FLAG_OVERLAP, gs.FLAG_NCCL_EXCHANGE, gs.FLAG_NCCL_EXCHANGE | gs.FLAG_OVERLAP):
         uid = gs.nccl_unique_id()
         res, errs = [None, None], []
 
@@ -308,6 +309,7 @@ def test_two_gpus_when_present(gs, oracle):
                     a = sim.accel()
                     sim.step(6)
                     e = sim.energy()
+                    assert sim.info.peer_exchange == (0 if flags & gs.FLAG_NCCL_EXCHANGE else 1)
                     res[rank] = (a, sim.download(), e, (sim.info.i_begin, sim.info.i_end))
             except Exception as ex:      # noqa: BLE001
                 errs.append(ex)
