@@ -42,7 +42,7 @@ UNIT = "interactions/s"
 def workload_config(n_gpus):
     return {"workload": "plummer_n1048576_euler", "n_bodies": N_BODIES, "eps": EPS, "dt": DT, "G": 1.0,
             "integrator": "symplectic-euler (reference: cuda.cu:73-76, mpi.c:206-215)", "interactions_per_step": N_BODIES * (N_BODIES - 1),
-            "partition": f"{n_gpus} x N/{n_gpus} i-bodies, NCCL all-gather of float4 positions per step"
+            "partition": f"{n_gpus} x N/{n_gpus} i-bodies, per-step exchange of 16 B/body positions over NVLink"
             if n_gpus > 1 else "single GPU",
             "l2": "flushed between timed steps (256 MiB write); positions 16 MiB"}
 

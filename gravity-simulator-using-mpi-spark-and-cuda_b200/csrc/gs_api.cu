@@ -202,7 +202,7 @@ int sync_velocities(gs_ctx* c) {
     return GS_OK;
 }
 
-// Measured on B200 at N = 1M (profiles/r2_variant_sweep_*.txt): softened -> R=6 x 256 threads (72.0 % general,
+// Measured on B200 at N = 1M (profiles/r1_variant_probe_n1048576.txt): softened -> R=6 x 256 threads (72.0 % general,
 // 78.7 % equal masses), cutoff -> R=8 x 256 threads (65.2 %).  R=6 has a 1536-body i-tile, which pads some
 // N / GPU-count combinations more than the 2048-body tile of R=8 does: charge each its padded work.
 int default_variant(int n, int world, int cut_mode) {
