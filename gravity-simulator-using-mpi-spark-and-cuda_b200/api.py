@@ -22,13 +22,14 @@ FLAG_TWO_PASS = 2
 FLAG_NO_UNIFORM_MASS = 4
 FLAG_OVERLAP = 8
 FLAG_NCCL_EXCHANGE = 16
+FLAG_COMPENSATED = 32
 NCCL_ID_BYTES = 128
 
 # every symbol include/gravsim.h declares (checked by the CPU tests)
 EXPORTED_SYMBOLS = [
     "gs_config_init", "gs_create", "gs_destroy", "gs_nccl_unique_id",
     "gs_upload_aos_f32", "gs_upload_aos_f64", "gs_download_aos_f32", "gs_download_aos_f64",
-    "gs_step", "gs_accel", "gs_energy", "gs_potential_energy_noalloc", "gs_sync", "gs_set_dt",
+    "gs_step", "gs_step_trajectory", "gs_accel", "gs_energy", "gs_potential_energy_noalloc", "gs_sync", "gs_set_dt",
     "gs_get_info", "gs_kernel_launches", "gs_last_cuda_error", "gs_strerror", "gs_version",
     "gs_host_alloc", "gs_host_free",
     "gs_plan_slice", "gs_plan_cta_range", "gs_plan_tile_owners", "gs_plan_tiles",
@@ -116,6 +117,7 @@ def lib():
     for f in ("gs_upload_aos_f32", "gs_upload_aos_f64", "gs_download_aos_f32", "gs_download_aos_f64"):
         getattr(L, f).argtypes = [C.c_void_p, C.c_void_p, C.c_int]
     L.gs_step.argtypes = [C.c_void_p, C.c_int]
+    L.gs_step_trajectory.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.POINTER(C.c_int)]
     L.gs_accel.argtypes = [C.c_void_p, C.c_void_p]
     L.gs_energy.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double)]
     L.gs_sync.argtypes = [C.c_void_p]
@@ -323,6 +325,16 @@ class GravSim:
     # -- hot path
     def step(self, nsteps=1):
         _check(lib().gs_step(self._ctx, int(nsteps)), "gs_step", self._ctx)
+
+    def step_trajectory(self, nsteps, every=1):
+        """Like step(), returning positions recorded every `every` steps: (nsteps // every, n, 3) float32
+        (what pyspark.py:104-121 collects as `trajectories`)."""
+        count = int(nsteps) // int(every)
+        out = np.empty((count, self.n, 3), dtype=np.float32)
+        got = C.c_int()
+        _check(lib().gs_step_trajectory(self._ctx, int(nsteps), int(every), out.ctypes.data, count, C.byref(got)),
+               "gs_step_trajectory", self._ctx)
+        return out[:got.value]
 
     def accel(self):
         """Accelerations (n_local, 3) float32 of this rank's bodies on the current snapshot."""

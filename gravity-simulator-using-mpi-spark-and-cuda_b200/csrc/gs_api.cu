@@ -25,6 +25,9 @@ struct gs_ctx {
     int cur = 0;
     float4* vel = nullptr;        // this rank's slice
     float4* vel_full = nullptr;   // world_size > 1: gathered velocities for download (lazy)
+    float4* pos_lo = nullptr;     // GS_FLAG_COMPENSATED: low-order words of this rank's positions / velocities
+    float4* vel_lo = nullptr;
+    float4* lo_full[2] = {nullptr, nullptr};   // ... gathered for download when world_size > 1 (lazy)
     float4* acc_local = nullptr;  // world_size > 1: accelerations from the local j-slice
     float4* acc_stage = nullptr;  // peer-memory mode: accelerations handed from the force kernel to the finish kernel
     float4* acc_out = nullptr;    // gs_accel output (lazy)
@@ -58,6 +61,12 @@ struct gs_ctx {
     uint32_t xstep = 0;                        // exchanges issued so far (same on every rank)
     bool wait_pending = false;                 // pos[cur] still needs the peers' flags before remote bodies are read
     unsigned long long comm_timeout_ns = 20000000000ull;
+    // trajectory recording (gs_step_trajectory): snapshots leave on a copy stream while the next steps run
+    cudaStream_t copy_stream = nullptr;
+    float4* h_snap[2] = {nullptr, nullptr};
+    cudaEvent_t ev_snap_ready[2] = {nullptr, nullptr}, ev_snap_done[2] = {nullptr, nullptr};
+    bool buf_copy_pending[2] = {false, false};   // pos[b] is still being read by a snapshot copy
+    int buf_copy_event[2] = {0, 0};
 };
 
 namespace {
@@ -123,11 +132,13 @@ int force_pass(gs_ctx* c, int final_mode, float kick, float drift, float4* acc_o
     p.drift_dt = drift;
     p.mu_uniform = c->mu_uniform;
     const int W = c->cfg.world_size;
-    PeerTargets peers;
-    peers.n = 0;
+    FinishExtras extras;
+    extras.peers.n = 0;
+    extras.pos_lo = c->pos_lo;
+    extras.vel_lo = c->vel_lo;
     if (c->p2p && final_mode == kFinalIntegrate) {   // fused exchange: the finish kernel stores into every peer's pos[nxt]
         for (int q = 0; q < W; ++q)
-            if (q != c->cfg.rank) peers.pos_new[peers.n++] = c->peer_pos[c->cur ^ 1][q];
+            if (q != c->cfg.rank) extras.peers.pos_new[extras.peers.n++] = c->peer_pos[c->cur ^ 1][q];
     }
     // two passes (own j-slice first, the rest once the peers' bodies are in): GS_FLAG_OVERLAP on several
     // GPUs, or GS_FLAG_TWO_PASS (same code path on one GPU, for tests)
@@ -138,12 +149,13 @@ int force_pass(gs_ctx* c, int final_mode, float kick, float drift, float4* acc_o
     // for EVERY tile (integration + stores into all peers' buffers in one kernel): the force kernel then
     // only leaves accelerations in acc_stage.
     auto run = [&](StepParams q, bool need_fixup) -> int {
-        const bool defer = c->p2p && q.final_mode == kFinalIntegrate;
+        const bool defer = (c->p2p && q.final_mode == kFinalIntegrate) ||
+                           (c->pos_lo != nullptr && q.final_mode != kFinalAccOut);   // compensated update lives there too
         StepParams f = q;
         if (defer) { f.final_mode = kFinalAccOut; f.acc_out = c->acc_stage; }
         GS_CUDA(c, launch_force(c->variant, c->cut_mode, f, c->grid, c->stream)); c->launches++;
         if (need_fixup || defer) {
-            GS_CUDA(c, launch_fixup(c->variant, q, c->grid, defer ? c->acc_stage : nullptr, defer ? &peers : nullptr,
+            GS_CUDA(c, launch_fixup(c->variant, q, c->grid, defer ? c->acc_stage : nullptr, defer ? &extras : nullptr,
                                     c->stream));
             c->launches++;
         }
@@ -305,7 +317,7 @@ int setup_peer_exchange(gs_ctx* c) {
     delete[] h_blobs;
     if (rc != GS_OK) return rc;
     if (all_ok) {
-        GS_CUDA(c, cudaMalloc((void**)&c->acc_stage, (size_t)c->slice * sizeof(float4)));
+        if (!c->acc_stage) GS_CUDA(c, cudaMalloc((void**)&c->acc_stage, (size_t)c->slice * sizeof(float4)));
         c->p2p = true;
     } else {
         close_peer_mappings(c);
@@ -436,6 +448,7 @@ void gs_destroy(gs_ctx* c) {
     cudaFree(c->flags); cudaFree(c->d_comm_err);
     if (c->comm) nccl_api().CommDestroy(c->comm);
     cudaFree(c->pos[0]); cudaFree(c->pos[1]); cudaFree(c->vel); cudaFree(c->vel_full);
+    cudaFree(c->pos_lo); cudaFree(c->vel_lo); cudaFree(c->lo_full[0]); cudaFree(c->lo_full[1]);
     cudaFree(c->acc_local); cudaFree(c->acc_stage); cudaFree(c->acc_out); cudaFree(c->partial); cudaFree(c->mass);
     cudaFree(c->d_aos); cudaFree(c->d_energy);
     if (c->h_energy) cudaFreeHost(c->h_energy);
@@ -445,6 +458,12 @@ void gs_destroy(gs_ctx* c) {
         if (c->ev_gather[b]) cudaEventDestroy(c->ev_gather[b]);
     if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
     if (c->comm_stream) cudaStreamDestroy(c->comm_stream);
+    if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
+    for (int b = 0; b < 2; ++b) {
+        if (c->h_snap[b]) cudaFreeHost(c->h_snap[b]);
+        if (c->ev_snap_ready[b]) cudaEventDestroy(c->ev_snap_ready[b]);
+        if (c->ev_snap_done[b]) cudaEventDestroy(c->ev_snap_done[b]);
+    }
     delete c;
 }
 
@@ -531,6 +550,10 @@ int gs_create(gs_ctx** out, const gs_config* cfg) {
         !dmalloc((void**)&c->mass, (size_t)c->n_pad * sizeof(double)) ||
         !dmalloc((void**)&c->d_energy, ((size_t)egrid * 5 + 8) * sizeof(double)))
         return fail(GS_ENOMEM);
+    if ((c->cfg.flags & GS_FLAG_COMPENSATED) &&
+        (!dmalloc((void**)&c->pos_lo, vel_bytes) || !dmalloc((void**)&c->vel_lo, vel_bytes) ||
+         (!c->acc_stage && !dmalloc((void**)&c->acc_stage, vel_bytes))))
+        return fail(GS_ENOMEM);
     if ((cfg->world_size > 1 || (c->cfg.flags & GS_FLAG_TWO_PASS)) && !dmalloc((void**)&c->acc_local, vel_bytes))
         return fail(GS_ENOMEM);
     if (cudaHostAlloc((void**)&c->h_energy, ((size_t)egrid * 5 + 8) * sizeof(double), cudaHostAllocDefault) !=
@@ -588,7 +611,7 @@ static int upload_common(gs_ctx* c, const void* host, int n, int record_bytes) {
     }
     c->cur = 0;
     GS_CUDA(c, launch_aos_to_packed(c->d_aos, record_bytes, n, c->n_pad, c->cfg.G, c->pos[0], c->vel, c->mass,
-                                    c->i_begin, c->slice, c->stream));
+                                    c->i_begin, c->slice, c->pos_lo, c->vel_lo, c->stream));
     c->launches++;
     // the other buffer must carry mu and the padding too: remote slices are filled by the exchange,
     // the own slice by the integrator, but the padding bodies of a single-GPU run are only ever
@@ -607,6 +630,8 @@ static int upload_common(gs_ctx* c, const void* host, int n, int record_bytes) {
             GS_CUDA(c, cudaEventRecord(c->ev_gather[0], c->comm_stream));
         }
     }
+    if (c->copy_stream) GS_CUDA(c, cudaStreamSynchronize(c->copy_stream));
+    c->buf_copy_pending[0] = c->buf_copy_pending[1] = false;
     c->uploaded = true;
     c->vel_synced = true;
     c->steps_done = 0;
@@ -616,25 +641,95 @@ static int upload_common(gs_ctx* c, const void* host, int n, int record_bytes) {
 int gs_upload_aos_f32(gs_ctx* ctx, const void* particles28, int n) { return upload_common(ctx, particles28, n, 28); }
 int gs_upload_aos_f64(gs_ctx* ctx, const void* particles56, int n) { return upload_common(ctx, particles56, n, 56); }
 
+static int one_step(gs_ctx* c) {
+    int rc;
+    const float dt = (float)c->cfg.dt;
+    const int nxt = c->cur ^ 1;
+    if (c->buf_copy_pending[nxt]) {      // a recorded snapshot of that buffer must have left before it is overwritten
+        GS_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_snap_done[c->buf_copy_event[nxt]], 0));
+        c->buf_copy_pending[nxt] = false;
+    }
+    float kick = dt;
+    if (c->cfg.integrator == GS_INTEGRATOR_LEAPFROG && c->vel_synced) kick = 0.5f * dt;   // opening half kick
+    if ((rc = force_pass(c, kFinalIntegrate, kick, dt, nullptr)) != GS_OK) return rc;
+    if ((rc = exchange_positions(c, nxt)) != GS_OK) return rc;
+    c->cur = nxt;
+    if (c->cfg.integrator == GS_INTEGRATOR_LEAPFROG) c->vel_synced = false;
+    c->steps_done++;
+    return GS_OK;
+}
+
 int gs_step(gs_ctx* c, int nsteps) {
     if (!c || nsteps < 0) return GS_EINVAL;
     if (!c->uploaded) return GS_ESTATE;
     int rc = set_device(c);
     if (rc != GS_OK) return rc;
-    const float dt = (float)c->cfg.dt;
-    for (int s = 0; s < nsteps; ++s) {
-        float kick = dt;
-        if (c->cfg.integrator == GS_INTEGRATOR_LEAPFROG && c->vel_synced) kick = 0.5f * dt;   // opening half kick
-        if ((rc = force_pass(c, kFinalIntegrate, kick, dt, nullptr)) != GS_OK) return rc;
-        const int nxt = c->cur ^ 1;
-        if ((rc = exchange_positions(c, nxt)) != GS_OK) return rc;
-        c->cur = nxt;
-        if (c->cfg.integrator == GS_INTEGRATOR_LEAPFROG) c->vel_synced = false;
-        c->steps_done++;
-    }
+    for (int s = 0; s < nsteps; ++s)
+        if ((rc = one_step(c)) != GS_OK) return rc;
     // order the last exchange on the caller-visible stream too, so an event recorded there after
     // gs_step covers every byte of the step (positions are then valid on every rank)
     if (c->cfg.world_size > 1 && nsteps > 0 && (rc = wait_positions(c)) != GS_OK) return rc;
+    return GS_OK;
+}
+
+static void unpack_snapshot(const float4* packed, int n, float* xyz) {
+    for (int i = 0; i < n; ++i) {
+        const float4 A = packed[2 * (i >> 1)], B = packed[2 * (i >> 1) + 1];
+        const bool odd = (i & 1) != 0;
+        xyz[3 * (size_t)i + 0] = odd ? A.y : A.x;
+        xyz[3 * (size_t)i + 1] = odd ? A.w : A.z;
+        xyz[3 * (size_t)i + 2] = odd ? B.y : B.x;
+    }
+}
+
+int gs_step_trajectory(gs_ctx* c, int nsteps, int every, float* xyz_host, int capacity_snapshots, int* n_snapshots) {
+    if (!c || nsteps < 0 || every < 1 || !xyz_host) return GS_EINVAL;
+    if (!c->uploaded) return GS_ESTATE;
+    const int count = nsteps / every;
+    if (count > capacity_snapshots) return GS_EINVAL;
+    int rc = set_device(c);
+    if (rc != GS_OK) return rc;
+    const size_t snap_bytes = (size_t)c->n_pad * sizeof(float4);
+    if (!c->copy_stream) {
+        GS_CUDA(c, cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+        for (int b = 0; b < 2; ++b) {
+            GS_CUDA(c, cudaHostAlloc((void**)&c->h_snap[b], snap_bytes, cudaHostAllocDefault));
+            GS_CUDA(c, cudaEventCreateWithFlags(&c->ev_snap_ready[b], cudaEventDisableTiming));
+            GS_CUDA(c, cudaEventCreateWithFlags(&c->ev_snap_done[b], cudaEventDisableTiming));
+        }
+    }
+    const size_t frame = (size_t)c->n * 3;
+    int taken = 0, unpacked = 0;
+    for (int s = 1; s <= nsteps; ++s) {
+        if ((rc = one_step(c)) != GS_OK) return rc;
+        if (s % every != 0) continue;
+        const int b = taken & 1;
+        if (taken >= 2) {                       // staging buffer b still holds snapshot taken-2: unpack it first
+            GS_CUDA(c, cudaEventSynchronize(c->ev_snap_done[b]));
+            unpack_snapshot(c->h_snap[b], c->n, xyz_host + frame * unpacked++);
+        }
+        if ((rc = wait_positions(c)) != GS_OK) return rc;            // every rank's bodies are in pos[cur]
+        GS_CUDA(c, cudaEventRecord(c->ev_snap_ready[b], c->stream));
+        GS_CUDA(c, cudaStreamWaitEvent(c->copy_stream, c->ev_snap_ready[b], 0));
+        GS_CUDA(c, cudaMemcpyAsync(c->h_snap[b], c->pos[c->cur], snap_bytes, cudaMemcpyDeviceToHost, c->copy_stream));
+        GS_CUDA(c, cudaEventRecord(c->ev_snap_done[b], c->copy_stream));
+        if (c->cfg.world_size > 1) {
+            // peers store into this buffer two steps from now, gated only by my step counter: keep it simple
+            // and let the engine's stream wait for the copy right away
+            GS_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_snap_done[b], 0));
+        } else {
+            c->buf_copy_pending[c->cur] = true;   // one_step() waits only when this buffer is about to be overwritten
+            c->buf_copy_event[c->cur] = b;
+        }
+        ++taken;
+    }
+    while (unpacked < taken) {
+        const int b = unpacked & 1;
+        GS_CUDA(c, cudaEventSynchronize(c->ev_snap_done[b]));
+        unpack_snapshot(c->h_snap[b], c->n, xyz_host + frame * unpacked++);
+    }
+    if (c->cfg.world_size > 1 && nsteps > 0 && (rc = wait_positions(c)) != GS_OK) return rc;
+    if (n_snapshots) *n_snapshots = taken;
     return GS_OK;
 }
 
@@ -713,6 +808,7 @@ static int download_common(gs_ctx* c, void* host, int n, int record_bytes) {
     if (rc != GS_OK) return rc;
     if ((rc = sync_velocities(c)) != GS_OK) return rc;
     const float4* vel_full = c->vel;
+    const float4 *pos_lo_full = c->pos_lo, *vel_lo_full = c->vel_lo;
     if (c->cfg.world_size > 1) {
         NcclApi& nc = nccl_api();
         if (!c->vel_full) GS_CUDA(c, cudaMalloc((void**)&c->vel_full, (size_t)c->n_pad * sizeof(float4)));
@@ -720,10 +816,20 @@ static int download_common(gs_ctx* c, void* host, int n, int record_bytes) {
         if (nc.AllGather(c->vel, c->vel_full, (size_t)c->slice * 4, ncclFloat, c->comm, c->stream) != ncclSuccess)
             return GS_ENCCL;
         vel_full = c->vel_full;
+        if (c->pos_lo) {
+            const float4* src[2] = {c->pos_lo, c->vel_lo};
+            for (int k = 0; k < 2; ++k) {
+                if (!c->lo_full[k]) GS_CUDA(c, cudaMalloc((void**)&c->lo_full[k], (size_t)c->n_pad * sizeof(float4)));
+                if (nc.AllGather(src[k], c->lo_full[k], (size_t)c->slice * 4, ncclFloat, c->comm, c->stream) != ncclSuccess)
+                    return GS_ENCCL;
+            }
+            pos_lo_full = c->lo_full[0]; vel_lo_full = c->lo_full[1];
+        }
     }
     const size_t bytes = (size_t)n * record_bytes;
     if ((rc = ensure_aos(c, bytes)) != GS_OK) return rc;
-    GS_CUDA(c, launch_packed_to_aos(c->pos[c->cur], vel_full, c->mass, n, c->d_aos, record_bytes, c->stream));
+    GS_CUDA(c, launch_packed_to_aos(c->pos[c->cur], vel_full, c->mass, n, c->d_aos, record_bytes, pos_lo_full,
+                                    vel_lo_full, c->stream));
     c->launches++;
     GS_CUDA(c, cudaMemcpyAsync(host, c->d_aos, bytes, cudaMemcpyDeviceToHost, c->stream));
     GS_CUDA(c, cudaStreamSynchronize(c->stream));

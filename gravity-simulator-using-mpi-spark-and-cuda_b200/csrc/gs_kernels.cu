@@ -75,9 +75,34 @@ __device__ __forceinline__ float rsqrt_approx(float x) {
 // integration).  Only the finishing kernel is built with PEERS = true: compiled into the force kernel the
 // extra loop perturbs ptxas' schedule of the hot inner loop (measured -2.5 %), so on several GPUs the
 // force kernel hands its accelerations to finish_kernel instead (16 B per body, negligible).
+// Error-free pieces of the compensated update (GS_FLAG_COMPENSATED): the state is kept as hi + lo fp32 pairs,
+// so x += v*dt no longer rounds to the 16 km ulp of a 3e11 m coordinate every step.
+__device__ __forceinline__ void two_sum(float a, float b, float& s, float& e) {
+    s = __fadd_rn(a, b);
+    const float bb = __fadd_rn(s, -a);
+    e = __fadd_rn(__fadd_rn(a, -__fadd_rn(s, -bb)), __fadd_rn(b, -bb));
+}
+// (hi, lo) += inc_hi + inc_lo
+__device__ __forceinline__ void comp_add(float& hi, float& lo, float inc_hi, float inc_lo) {
+    float s, e;
+    two_sum(hi, inc_hi, s, e);
+    e = __fadd_rn(e, __fadd_rn(lo, inc_lo));
+    hi = __fadd_rn(s, e);
+    lo = __fadd_rn(e, -__fadd_rn(hi, -s));
+}
+// v += a*kick ; x += v*drift, both compensated
+__device__ __forceinline__ void comp_step(float a, float kick, float drift, bool do_drift, float& v, float& vlo,
+                                          float& x, float& xlo) {
+    const float dv = __fmul_rn(a, kick);
+    comp_add(v, vlo, dv, __fmaf_rn(a, kick, -dv));
+    if (!do_drift) return;
+    const float dx = __fmul_rn(v, drift);
+    comp_add(x, xlo, dx, __fadd_rn(__fmaf_rn(v, drift, -dx), __fmul_rn(vlo, drift)));
+}
+
 template <bool PEERS>
 __device__ __forceinline__ void finish_pair(const StepParams& p, int pair_local, float4 a0, float4 a1,
-                                            const PeerTargets* peers = nullptr) {
+                                            const FinishExtras* ex = nullptr) {
     if (p.acc_in != nullptr) {
         const float4 b0 = p.acc_in[2 * pair_local], b1 = p.acc_in[2 * pair_local + 1];
         a0.x += b0.x; a0.y += b0.y; a0.z += b0.z;
@@ -95,20 +120,36 @@ __device__ __forceinline__ void finish_pair(const StepParams& p, int pair_local,
     const int pair_global = (p.i_begin >> 1) + pair_local;
     float4 VA = p.vel[2 * pair_local], VB = p.vel[2 * pair_local + 1];
     float4 PA = p.pos_old[2 * pair_global], PB = p.pos_old[2 * pair_global + 1];
-    VA.x = fmaf(a0.x, p.kick_dt, VA.x); VA.y = fmaf(a1.x, p.kick_dt, VA.y);
-    VA.z = fmaf(a0.y, p.kick_dt, VA.z); VA.w = fmaf(a1.y, p.kick_dt, VA.w);
-    VB.x = fmaf(a0.z, p.kick_dt, VB.x); VB.y = fmaf(a1.z, p.kick_dt, VB.y);
-    p.vel[2 * pair_local] = VA; p.vel[2 * pair_local + 1] = VB;
-    if (p.final_mode == kFinalKickOnly) return;
-    PA.x = fmaf(VA.x, p.drift_dt, PA.x); PA.y = fmaf(VA.y, p.drift_dt, PA.y);
-    PA.z = fmaf(VA.z, p.drift_dt, PA.z); PA.w = fmaf(VA.w, p.drift_dt, PA.w);
-    PB.x = fmaf(VB.x, p.drift_dt, PB.x); PB.y = fmaf(VB.y, p.drift_dt, PB.y);
+    if (PEERS && ex->pos_lo != nullptr) {   // compensated integration (finish kernel only)
+        float4 LA = ex->pos_lo[2 * pair_local], LB = ex->pos_lo[2 * pair_local + 1];
+        float4 WA = ex->vel_lo[2 * pair_local], WB = ex->vel_lo[2 * pair_local + 1];
+        const bool drift = (p.final_mode != kFinalKickOnly);
+        comp_step(a0.x, p.kick_dt, p.drift_dt, drift, VA.x, WA.x, PA.x, LA.x);
+        comp_step(a1.x, p.kick_dt, p.drift_dt, drift, VA.y, WA.y, PA.y, LA.y);
+        comp_step(a0.y, p.kick_dt, p.drift_dt, drift, VA.z, WA.z, PA.z, LA.z);
+        comp_step(a1.y, p.kick_dt, p.drift_dt, drift, VA.w, WA.w, PA.w, LA.w);
+        comp_step(a0.z, p.kick_dt, p.drift_dt, drift, VB.x, WB.x, PB.x, LB.x);
+        comp_step(a1.z, p.kick_dt, p.drift_dt, drift, VB.y, WB.y, PB.y, LB.y);
+        p.vel[2 * pair_local] = VA; p.vel[2 * pair_local + 1] = VB;
+        ex->vel_lo[2 * pair_local] = WA; ex->vel_lo[2 * pair_local + 1] = WB;
+        if (!drift) return;
+        ex->pos_lo[2 * pair_local] = LA; ex->pos_lo[2 * pair_local + 1] = LB;
+    } else {
+        VA.x = fmaf(a0.x, p.kick_dt, VA.x); VA.y = fmaf(a1.x, p.kick_dt, VA.y);
+        VA.z = fmaf(a0.y, p.kick_dt, VA.z); VA.w = fmaf(a1.y, p.kick_dt, VA.w);
+        VB.x = fmaf(a0.z, p.kick_dt, VB.x); VB.y = fmaf(a1.z, p.kick_dt, VB.y);
+        p.vel[2 * pair_local] = VA; p.vel[2 * pair_local + 1] = VB;
+        if (p.final_mode == kFinalKickOnly) return;
+        PA.x = fmaf(VA.x, p.drift_dt, PA.x); PA.y = fmaf(VA.y, p.drift_dt, PA.y);
+        PA.z = fmaf(VA.z, p.drift_dt, PA.z); PA.w = fmaf(VA.w, p.drift_dt, PA.w);
+        PB.x = fmaf(VB.x, p.drift_dt, PB.x); PB.y = fmaf(VB.y, p.drift_dt, PB.y);
+    }
     p.pos_new[2 * pair_global] = PA; p.pos_new[2 * pair_global + 1] = PB;   // PB.zw = mu, unchanged
     if (PEERS) {
         // same 32 B to every peer over NVLink (replaces MPI_Allgatherv, mpi.c:227-231); made visible to the
         // peers by the flag protocol of signal_peers_kernel / wait_flags_kernel
-        for (int q = 0; q < peers->n; ++q) {
-            float4* dst = peers->pos_new[q] + 2 * (size_t)pair_global;
+        for (int q = 0; q < ex->peers.n; ++q) {
+            float4* dst = ex->peers.pos_new[q] + 2 * (size_t)pair_global;
             dst[0] = PA; dst[1] = PB;
         }
     }
@@ -326,7 +367,7 @@ __global__ void __launch_bounds__(THREADS, MINB) force_step_kernel(const StepPar
 //                   then the force kernel only stored their accelerations there and this kernel finishes
 //                   them too (multi-GPU: integration + peer stores happen here, for every body).
 __global__ void __launch_bounds__(256) fixup_kernel(const StepParams p, int grid_main, int ITILE,
-                                                    const float4* __restrict__ whole_acc, const PeerTargets peers) {
+                                                    const float4* __restrict__ whole_acc, const FinishExtras ex) {
     const int pair_local = blockIdx.x * blockDim.x + threadIdx.x;
     if (pair_local >= p.ni_tiles * (ITILE / 2)) return;
     const int64_t it = pair_local / (ITILE / 2);
@@ -336,7 +377,7 @@ __global__ void __launch_bounds__(256) fixup_kernel(const StepParams p, int grid
         if (whole_acc == nullptr) return;   // finished inside the force kernel
         StepParams pw = p;
         pw.acc_in = nullptr;                // the force kernel already added the upstream accelerations
-        finish_pair<true>(pw, pair_local, whole_acc[2 * pair_local], whole_acc[2 * pair_local + 1], &peers);
+        finish_pair<true>(pw, pair_local, whole_acc[2 * pair_local], whole_acc[2 * pair_local + 1], &ex);
         return;
     }
     const int64_t U = (int64_t)p.ni_tiles * p.nj_tiles;
@@ -349,7 +390,7 @@ __global__ void __launch_bounds__(256) fixup_kernel(const StepParams p, int grid
         a0.x += s0.x; a0.y += s0.y; a0.z += s0.z;
         a1.x += s1.x; a1.y += s1.y; a1.z += s1.z;
     }
-    finish_pair<true>(p, pair_local, a0, a1, &peers);
+    finish_pair<true>(p, pair_local, a0, a1, &ex);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -426,14 +467,14 @@ cudaError_t launch_force(int variant, int cut_mode, const StepParams& p, int gri
 }
 
 cudaError_t launch_fixup(int variant, const StepParams& p, int grid_main, const float4* whole_acc,
-                         const PeerTargets* peers, cudaStream_t s) {
+                         const FinishExtras* extras, cudaStream_t s) {
     VariantInfo vi;
     if (!variant_info(variant, &vi)) return cudaErrorInvalidValue;
     const int pairs = p.ni_tiles * (vi.i_tile / 2);
     const int blocks = (pairs + 255) / 256;
-    PeerTargets none;
-    none.n = 0;
-    fixup_kernel<<<blocks, 256, 0, s>>>(p, grid_main, vi.i_tile, whole_acc, peers ? *peers : none);
+    FinishExtras none;
+    none.peers.n = 0; none.pos_lo = nullptr; none.vel_lo = nullptr;
+    fixup_kernel<<<blocks, 256, 0, s>>>(p, grid_main, vi.i_tile, whole_acc, extras ? *extras : none);
     return cudaGetLastError();
 }
 
@@ -480,10 +521,12 @@ cudaError_t launch_wait_flags(const uint32_t* my_flags, int world, int my_rank, 
 // ------------------------------------------------------------------------------------------------
 template <typename T>
 __global__ void aos_to_packed_kernel(const T* __restrict__ aos, int n, int n_pad, double G, float4* pos,
-                                     float4* vel_local, double* mass, int i_begin, int n_local_pad) {
+                                     float4* vel_local, double* mass, int i_begin, int n_local_pad,
+                                     float4* pos_lo_local, float4* vel_lo_local) {
     const int pair = blockIdx.x * blockDim.x + threadIdx.x;
     if (pair >= n_pad / 2) return;
     float x[2], y[2], z[2], vx[2], vy[2], vz[2], mu[2];
+    float lo[2][6];
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
         const int i = 2 * pair + h;
@@ -491,12 +534,17 @@ __global__ void aos_to_packed_kernel(const T* __restrict__ aos, int n, int n_pad
             const T* r = aos + (size_t)i * 7;
             x[h] = (float)r[0]; y[h] = (float)r[1]; z[h] = (float)r[2];
             vx[h] = (float)r[3]; vy[h] = (float)r[4]; vz[h] = (float)r[5];
+            const float hi[6] = {x[h], y[h], z[h], vx[h], vy[h], vz[h]};
+#pragma unroll
+            for (int c = 0; c < 6; ++c) lo[h][c] = (float)((double)r[c] - (double)hi[c]);   // 0 for f32 records
             const double m = (double)r[6];
             mu[h] = (float)(G * m);          // never form m_i*m_j: G*m <= 1.33e20 fits fp32
             mass[i] = m;
         } else {                             // padding: massless, at rest, so far away that rinv^3 underflows to 0
             x[h] = y[h] = z[h] = kPadPosition;
             vx[h] = vy[h] = vz[h] = mu[h] = 0.f;
+#pragma unroll
+            for (int c = 0; c < 6; ++c) lo[h][c] = 0.f;
             mass[i] = 0.0;
         }
     }
@@ -507,52 +555,62 @@ __global__ void aos_to_packed_kernel(const T* __restrict__ aos, int n, int n_pad
         const int pl = (first - i_begin) >> 1;
         vel_local[2 * pl] = make_float4(vx[0], vx[1], vy[0], vy[1]);
         vel_local[2 * pl + 1] = make_float4(vz[0], vz[1], 0.f, 0.f);
+        if (pos_lo_local != nullptr) {
+            pos_lo_local[2 * pl] = make_float4(lo[0][0], lo[1][0], lo[0][1], lo[1][1]);
+            pos_lo_local[2 * pl + 1] = make_float4(lo[0][2], lo[1][2], 0.f, 0.f);
+            vel_lo_local[2 * pl] = make_float4(lo[0][3], lo[1][3], lo[0][4], lo[1][4]);
+            vel_lo_local[2 * pl + 1] = make_float4(lo[0][5], lo[1][5], 0.f, 0.f);
+        }
     }
 }
 
 template <typename T>
 __global__ void packed_to_aos_kernel(const float4* __restrict__ pos, const float4* __restrict__ vel,
-                                     const double* __restrict__ mass, int n, T* aos) {
+                                     const double* __restrict__ mass, int n, T* aos,
+                                     const float4* __restrict__ pos_lo, const float4* __restrict__ vel_lo) {
     const int pair = blockIdx.x * blockDim.x + threadIdx.x;
     if (2 * pair >= n) return;
     const float4 PA = pos[2 * pair], PB = pos[2 * pair + 1];
     const float4 VA = vel[2 * pair], VB = vel[2 * pair + 1];
+    float4 LA = make_float4(0.f, 0.f, 0.f, 0.f), LB = LA, WA = LA, WB = LA;
+    if (pos_lo != nullptr) { LA = pos_lo[2 * pair]; LB = pos_lo[2 * pair + 1]; WA = vel_lo[2 * pair]; WB = vel_lo[2 * pair + 1]; }
     {
         T* r = aos + (size_t)(2 * pair) * 7;
-        r[0] = (T)PA.x; r[1] = (T)PA.z; r[2] = (T)PB.x;
-        r[3] = (T)VA.x; r[4] = (T)VA.z; r[5] = (T)VB.x;
+        r[0] = (T)((double)PA.x + LA.x); r[1] = (T)((double)PA.z + LA.z); r[2] = (T)((double)PB.x + LB.x);
+        r[3] = (T)((double)VA.x + WA.x); r[4] = (T)((double)VA.z + WA.z); r[5] = (T)((double)VB.x + WB.x);
         r[6] = (T)mass[2 * pair];
     }
     if (2 * pair + 1 < n) {
         T* r = aos + (size_t)(2 * pair + 1) * 7;
-        r[0] = (T)PA.y; r[1] = (T)PA.w; r[2] = (T)PB.y;
-        r[3] = (T)VA.y; r[4] = (T)VA.w; r[5] = (T)VB.y;
+        r[0] = (T)((double)PA.y + LA.y); r[1] = (T)((double)PA.w + LA.w); r[2] = (T)((double)PB.y + LB.y);
+        r[3] = (T)((double)VA.y + WA.y); r[4] = (T)((double)VA.w + WA.w); r[5] = (T)((double)VB.y + WB.y);
         r[6] = (T)mass[2 * pair + 1];
     }
 }
 
 cudaError_t launch_aos_to_packed(const void* aos, int record_bytes, int n, int n_pad, double G, float4* pos,
                                  float4* vel_local, double* mass, int i_begin, int n_local_pad,
-                                 cudaStream_t s) {
+                                 float4* pos_lo_local, float4* vel_lo_local, cudaStream_t s) {
     const int blocks = (n_pad / 2 + 255) / 256;
     if (record_bytes == 28)
         aos_to_packed_kernel<float><<<blocks, 256, 0, s>>>((const float*)aos, n, n_pad, G, pos, vel_local, mass,
-                                                           i_begin, n_local_pad);
+                                                           i_begin, n_local_pad, pos_lo_local, vel_lo_local);
     else if (record_bytes == 56)
         aos_to_packed_kernel<double><<<blocks, 256, 0, s>>>((const double*)aos, n, n_pad, G, pos, vel_local, mass,
-                                                            i_begin, n_local_pad);
+                                                            i_begin, n_local_pad, pos_lo_local, vel_lo_local);
     else
         return cudaErrorInvalidValue;
     return cudaGetLastError();
 }
 
 cudaError_t launch_packed_to_aos(const float4* pos, const float4* vel_full, const double* mass, int n, void* aos,
-                                 int record_bytes, cudaStream_t s) {
+                                 int record_bytes, const float4* pos_lo_full, const float4* vel_lo_full,
+                                 cudaStream_t s) {
     const int blocks = ((n + 1) / 2 + 255) / 256;
     if (record_bytes == 28)
-        packed_to_aos_kernel<float><<<blocks, 256, 0, s>>>(pos, vel_full, mass, n, (float*)aos);
+        packed_to_aos_kernel<float><<<blocks, 256, 0, s>>>(pos, vel_full, mass, n, (float*)aos, pos_lo_full, vel_lo_full);
     else if (record_bytes == 56)
-        packed_to_aos_kernel<double><<<blocks, 256, 0, s>>>(pos, vel_full, mass, n, (double*)aos);
+        packed_to_aos_kernel<double><<<blocks, 256, 0, s>>>(pos, vel_full, mass, n, (double*)aos, pos_lo_full, vel_lo_full);
     else
         return cudaErrorInvalidValue;
     return cudaGetLastError();

@@ -45,6 +45,9 @@ struct StepParams {
 // Peers' pos_new buffers (NVLink peer memory, same indexing as StepParams::pos_new).  Kept out of StepParams:
 // growing the force kernel's parameter block changes ptxas' schedule of its inner loop (measured -2.5 %).
 struct PeerTargets { int n; float4* pos_new[kMaxPeers]; };
+// What only the finish kernel needs: peers, and the low-order words of the compensated integration
+// (GS_FLAG_COMPENSATED: x = pos + pos_lo, v = vel + vel_lo; null otherwise).  Local (slice) indexing.
+struct FinishExtras { PeerTargets peers; float4* pos_lo; float4* vel_lo; };
 
 size_t force_smem_bytes();
 // Max resident CTAs per SM of the force kernel for this variant / cut mode, and its registers.
@@ -54,7 +57,7 @@ cudaError_t launch_force(int variant, int cut_mode, const StepParams& p, int gri
 // or writes accelerations).  `grid_main` is the force kernel's grid.
 // whole_acc != nullptr: also finish the whole tiles, whose accelerations the force kernel left there.
 cudaError_t launch_fixup(int variant, const StepParams& p, int grid_main, const float4* whole_acc,
-                         const PeerTargets* peers, cudaStream_t s);
+                         const FinishExtras* extras, cudaStream_t s);
 
 // Peer-memory exchange (replaces the per-step collective when every GPU can map its peers' buffers):
 // the integrating epilogue stores new positions straight into every peer's position buffer over
@@ -68,11 +71,14 @@ cudaError_t launch_wait_flags(const uint32_t* my_flags, int world, int my_rank, 
 
 // AoS <-> packed-pair conversion on the device. `aos` is the raw byte image of the reference's
 // 28-byte (f32) or 56-byte (f64) records.  Bodies >= n are padding (mu = 0, at the origin).
+// pos_lo_local / vel_lo_local (nullable): low-order words, i.e. what rounding the record to fp32 dropped.
 cudaError_t launch_aos_to_packed(const void* aos, int record_bytes, int n, int n_pad, double G,
                                  float4* pos, float4* vel_local, double* mass, int i_begin,
-                                 int n_local_pad, cudaStream_t s);
+                                 int n_local_pad, float4* pos_lo_local, float4* vel_lo_local, cudaStream_t s);
+// pos_lo_full / vel_lo_full (nullable): added back in (exact for f64 records).
 cudaError_t launch_packed_to_aos(const float4* pos, const float4* vel_full, const double* mass,
-                                 int n, void* aos, int record_bytes, cudaStream_t s);
+                                 int n, void* aos, int record_bytes, const float4* pos_lo_full,
+                                 const float4* vel_lo_full, cudaStream_t s);
 
 // Energy diagnostics (fp64 accumulation).  potential: out_partials[gridDim] doubles, one per
 // CTA, of sum_i mu_i * sum_{j != i} mu_j / sqrt(r^2 + eps^2) over this rank's i-bodies (the caller

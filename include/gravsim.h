@@ -71,6 +71,9 @@ typedef struct gs_config {
 #define GS_FLAG_NO_UNIFORM_MASS 4u /* keep the general kernel even when all masses are equal        */
 #define GS_FLAG_OVERLAP    8u   /* multi-GPU: own j-slice first, remote slices after the exchange  */
 #define GS_FLAG_NCCL_EXCHANGE 16u /* multi-GPU: per-step ncclAllGather instead of peer-memory stores */
+#define GS_FLAG_COMPENSATED 32u /* positions and velocities as hi+lo fp32 pairs: the integration no longer
+                                   rounds to the state's fp32 ulp each step (forces stay fp32); f64 records
+                                   keep their low-order bits through upload/download                    */
 
 typedef struct gs_info {
     int32_t n, n_pad;             /* bodies, padded bodies (multiple of the tile sizes)          */
@@ -118,6 +121,14 @@ int gs_download_aos_f64(gs_ctx *ctx, void *particles56, int n);
  * same snapshot (synchronous step; see DESIGN.md on mpi.c's in-place order).  Asynchronous:
  * returns after enqueueing; no per-step host synchronisation or D2H. */
 int gs_step(gs_ctx *ctx, int nsteps);
+
+/* gs_step that also records the positions of all n bodies every `every` steps (after steps every, 2*every,
+ * ...): xyz_host receives nsteps/every frames of n x 3 floats (at most capacity_snapshots, else GS_EINVAL).
+ * Takes the place of the per-step `trajectories.append(positions)` of pyspark.py:104-121 (cuda.cu and mpi.c
+ * keep final positions only).  Frames leave through a copy stream and pinned staging while the following
+ * steps compute; the call returns when every frame is in xyz_host. */
+int gs_step_trajectory(gs_ctx *ctx, int nsteps, int every, float *xyz_host, int capacity_snapshots,
+                       int *n_snapshots);
 
 /* Accelerations of THIS rank's bodies [i_begin, i_end) on the current frozen snapshot, 3 floats
  * per body; state unchanged.  The reference only exposes forces[] via the D2H at cuda.cu:160

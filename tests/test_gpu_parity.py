@@ -239,6 +239,43 @@ def test_energy_si_units_cutoff(gs, oracle):
     assert np.abs(mom - omom).max() <= 1e-6 * np.abs(b[:, 6:7] * b[:, 3:6]).sum()
 
 
+def test_compensated_integration_closes_the_fp32_state_gap(gs, oracle):
+    # GS_FLAG_COMPENSATED keeps x and v as hi+lo fp32 pairs: 100 steps at N=4096 (BASELINE configs[0]) land
+    # ~10x closer to the fp64 synchronous oracle than plain fp32 state, and f64 records
+    # survive upload/download beyond fp32 resolution.
+    b = gs.ic_reference_uniform(4096, seed=1234).astype(np.float64)
+    b[3:, :3] += np.random.default_rng(1).uniform(-1000.0, 1000.0, (4093, 3))     # not fp32-representable any more
+    ref = oracle.run_sync(b, 3600.0, 100)
+    errs = {}
+    for flags in (0, gs.FLAG_COMPENSATED, gs.FLAG_COMPENSATED | gs.FLAG_TWO_PASS):
+        with gs.GravSim(4096, dt=3600.0, flags=flags) as sim:
+            sim.upload(b)
+            if flags:
+                assert np.abs(sim.download(np.float64)[:, :3] - b[:, :3]).max() <= 1e-2    # metres, of 3e11
+            sim.step(100)
+            out = sim.download(np.float64)
+        errs[flags] = _traj_err(out, ref)
+    # what remains is the fp32 force error (~1e-6 relative) integrated twice, largest for bodies close to the Sun
+    assert errs[gs.FLAG_COMPENSATED][0] <= 2.5e-6 and errs[gs.FLAG_COMPENSATED][0] <= 0.2 * errs[0][0]
+    assert errs[gs.FLAG_COMPENSATED | gs.FLAG_TWO_PASS][0] <= 2.5e-6
+
+
+def test_trajectory_recording(gs):
+    b = gs.ic_reference_uniform(3001, seed=2)
+    with gs.GravSim(3001) as sim:
+        sim.upload(b)
+        frames = sim.step_trajectory(11, every=2)              # frames after steps 2, 4, 6, 8, 10
+        final = sim.download()
+    assert frames.shape == (5, 3001, 3)
+    with gs.GravSim(3001) as sim:
+        sim.upload(b)
+        for k in range(5):
+            sim.step(2)
+            assert np.array_equal(sim.download()[:, :3], frames[k])
+        sim.step(1)
+        assert np.array_equal(sim.download(), final)
+
+
 # ---- boundary behaviour -------------------------------------------------------------------------------
 def test_round_trip_accel_is_pure_and_deterministic(gs):
     b = gs.ic_reference_uniform(2500, seed=9)
@@ -298,7 +335,7 @@ def test_two_gpus_when_present(gs, oracle):
     b = gs.ic_reference_uniform(n, seed=31)
     ref = oracle.run_sync(b.astype(np.float64), 3600.0, 6)
     # peer-memory exchange (default), with the two-pass overlap schedule, and the NCCL all-gather fallback
-    for flags in (0, gs.FLAG_OVERLAP, gs.FLAG_NCCL_EXCHANGE, gs.FLAG_NCCL_EXCHANGE | gs.FLAG_OVERLAP):
+    for flags in (0, gs.FLAG_OVERLAP, gs.FLAG_NCCL_EXCHANGE, gs.FLAG_NCCL_EXCHANGE | gs.FLAG_OVERLAP, gs.FLAG_COMPENSATED):
         uid = gs.nccl_unique_id()
         res, errs = [None, None], []
 
@@ -310,7 +347,10 @@ def test_two_gpus_when_present(gs, oracle):
                     sim.step(6)
                     e = sim.energy()
                     assert sim.info.peer_exchange == (0 if flags & gs.FLAG_NCCL_EXCHANGE else 1)
-                    res[rank] = (a, sim.download(), e, (sim.info.i_begin, sim.info.i_end))
+                    out = sim.download()
+                    frames = sim.step_trajectory(2, every=1)                 # collective, like step()
+                    assert np.array_equal(frames[-1], sim.download()[:, :3])
+                    res[rank] = (a, out, e, (sim.info.i_begin, sim.info.i_end))
             except Exception as ex:      # noqa: BLE001
                 errs.append(ex)
         ts = [threading.Thread(target=work, args=(r,)) for r in range(2)]
