@@ -225,7 +225,7 @@ int default_variant(int n, int world, int cut_mode) {
     // small problems: too few (i-tile x j-tile) units to feed 148 SMs -> 512-body i-tiles, 4 CTAs per SM
     const int64_t units6 = ((int64_t)pad6 / world / 1536) * (pad6 / kJTile);
     if (units6 < 8 * 148) return 10;
-    if (cut_mode == kCutoff) return 3;
+    if (cut_mode != kSoftened) return 3;
     const double cost6 = (double)pad6 * pad6, cost3 = (double)pad3 * pad3 / 0.98;
     return cost6 <= cost3 ? 6 : 3;
 }
@@ -497,7 +497,9 @@ int gs_create(gs_ctx** out, const gs_config* cfg) {
     if (prop.major < 10) return fail(GS_ENOGPU);   // sm_100a code only
     c->sm_count = prop.multiProcessorCount;
 
-    c->cut_mode = (cfg->eps > 0.0) ? kSoftened : kCutoff;
+    c->cut_mode = (cfg->eps > 0.0) ? kSoftened : kCutoffTracked;
+    const char* ecm = getenv("GRAVSIM_CUTMODE");                        // "select" | "tracked": tests, A/B runs
+    if (c->cut_mode != kSoftened && ecm && !strcmp(ecm, "select")) c->cut_mode = kCutoff;
     c->variant = cfg->variant;
     if (c->variant == 0) {
         const char* ev = getenv("GRAVSIM_VARIANT");
@@ -508,9 +510,8 @@ int gs_create(gs_ctx** out, const gs_config* cfg) {
     c->R = vi.R;
     c->threads = vi.threads;
     c->i_tile = vi.i_tile;
-    c->cut_mode = (cfg->eps > 0.0) ? kSoftened : kCutoff;
     c->eps2 = (float)(cfg->eps * cfg->eps);
-    c->cut2 = (c->cut_mode == kCutoff) ? 1e-20f : 0.f;   // (1e-10)^2: cuda.cu:39, mpi.c:64
+    c->cut2 = (c->cut_mode != kSoftened) ? 1e-20f : 0.f;   // (1e-10)^2: cuda.cu:39, mpi.c:64
 
     c->n = cfg->n;
     int ib = 0, ie = 0;
@@ -528,6 +529,24 @@ int gs_create(gs_ctx** out, const gs_config* cfg) {
     const char* eg = getenv("GRAVSIM_GRID");
     if (eg && atoi(eg) > 0 && atoi(eg) <= c->grid) c->grid = atoi(eg);
 
+    if (c->cut_mode == kCutoffTracked && !(ecm && !strcmp(ecm, "tracked"))) {
+        // The tracked mode recomputes the i_tile/j_tile "diagonal" units of every i-tile (those that contain the
+        // bodies themselves) with the select.  The static partition does not know that: when a CTA only has a few
+        // dozen units, the CTAs holding diagonal units become a tail (N = 65,536: +14 %).  Use the plain select
+        // kernel (65 % of peak instead of 67 %) unless the extra work is below 1 % of a CTA's share.
+        const double units_per_cta = (double)(c->slice / c->i_tile) * (c->n_pad / kJTile) / c->grid;
+        if ((double)(c->i_tile / kJTile) > 0.01 * units_per_cta) {
+            c->cut_mode = kCutoff;
+            int ctas = 0, regs = 0, ctas2 = 0, regs2 = 0;
+            e = force_kernel_occupancy(c->variant, c->cut_mode, false, &ctas, &regs);
+            if (e == cudaSuccess) e = force_kernel_occupancy(c->variant, c->cut_mode, true, &ctas2, &regs2);
+            if (e != cudaSuccess || ctas < 1 || ctas2 < 1) { c->last_cuda_error = (int)e; return fail(GS_ECUDA); }
+            c->ctas_per_sm = ctas < ctas2 ? ctas : ctas2;
+            c->regs = regs;
+            c->grid = c->sm_count * c->ctas_per_sm;
+            if (eg && atoi(eg) > 0 && atoi(eg) <= c->grid) c->grid = atoi(eg);
+        }
+    }
     {
         const int64_t ni = c->slice / c->i_tile, nj = c->n_pad / kJTile, njl = c->slice / kJTile;
         c->split_full = any_split(ni, nj, c->grid);

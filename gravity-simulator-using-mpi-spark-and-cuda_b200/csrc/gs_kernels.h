@@ -9,7 +9,9 @@ namespace gs {
 enum FinalMode : int { kFinalIntegrate = 0,   // v += a*kick_dt; x += v*drift_dt -> pos_new
                        kFinalAccOut = 1,      // write accelerations, state untouched
                        kFinalKickOnly = 2 };  // v += a*kick_dt only (leapfrog velocity synchronisation)
-enum CutMode : int { kSoftened = 0, kCutoff = 1 };   // eps > 0  /  eps == 0 (reference r<1e-10 rule)
+enum CutMode : int { kSoftened = 0,        // eps > 0
+                     kCutoff = 1,          // eps == 0: reference r<1e-10 rule by a select on every interaction
+                     kCutoffTracked = 2 }; // eps == 0: same result; select-free fast pass + exact redo of the rare tiles
 
 // Kernel variants (gs_config.variant / env GRAVSIM_VARIANT): i-bodies per thread R, CTA size, inner
 // unroll, packed f32x2 or scalar arithmetic.  The table lives in gs_kernels.cu (GS_VARIANTS).

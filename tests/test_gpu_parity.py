@@ -97,6 +97,28 @@ def test_accel_1M_full_size_properties(gs, oracle):     # BASELINE.json configs[
     assert rel.max() <= ACC_TOL
 
 
+@pytest.mark.parametrize("cutmode", ["select", "tracked"])
+def test_both_cutoff_implementations(gs, oracle, cutmode, monkeypatch):
+    # eps == 0 has two kernels with identical semantics: a select on every interaction, and a select-free
+    # pass that tracks the smallest r^2 and redoes the rare tiles exactly (picked by problem size)
+    monkeypatch.setenv("GRAVSIM_CUTMODE", cutmode)
+    g = golden("coincident3.npz")
+    assert rel_err(gpu_accel(gs, g["bodies"].astype(np.float32)), g["accel"]).max() <= ACC_TOL
+    tiny = np.array([[1e-11, 0, 0, 0, 0, 0, 1e3], [5e-11, 0, 0, 0, 0, 0, 2e3], [1.0, 0, 0, 0, 0, 0, 3e3],
+                     [0, 2.0, 0, 0, 0, 0, 0.0]], dtype=np.float32)
+    ref = oracle.accel_subset(tiny.astype(np.float64), np.arange(4), massfree=True)[0]
+    a = gpu_accel(gs, tiny)
+    assert np.isfinite(a).all() and rel_err(a, ref).max() <= ACC_TOL
+    for variant in (0, 1, 6, 10):
+        b = gs.ic_reference_uniform(4100, seed=50 + variant)
+        b[7] = b[3]                                        # a coincident pair in the middle of a tile
+        a = gpu_accel(gs, b, variant=variant)
+        assert np.isfinite(a).all() and rel_err(a, oracle.accel(b.astype(np.float64))).max() <= ACC_TOL
+    p = gs.ic_plummer(3000, seed=1)                        # equal masses + eps == 0: hoisted-mass kernel, cutoff rule
+    ref = oracle.accel_subset(p.astype(np.float64), np.arange(3000), G=1.0, eps=0.0, massfree=True)[0]
+    assert rel_err(gpu_accel(gs, p, G=1.0), ref).max() <= 5e-5
+
+
 def test_fp32_range_sun_and_heavy_body(gs, oracle):
     # the case cuda.cu:41 fails: (G*m_i)*m_j overflows fp32 for the Sun
     b = np.array([[0, 0, 0, 0, 0, 0, 1.989e30], [1e11, 0, 0, 0, 0, 0, 1e25], [-3e11, 1e10, 0, 0, 0, 0, 1e25]],
