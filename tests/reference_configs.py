@@ -4,7 +4,8 @@
   configs[1]: N=65,536 bodies, fp32, 1000 steps on 1 B200 vs reference cuda.cu (fewer steps: it is slow,
               and its output is non-finite -- timing comparator only)
 
-Run on the GPU box:  python tools/run_reference_configs.py > gpurun_out/reference_configs.json
+Lives under tests/ because it drives the checkers in oracle/ (only tests, smoke() and bench.py's baseline legs may).
+Run on the GPU box:  python tests/reference_configs.py > gpurun_out/reference_configs.json
 """
 import json
 import os

@@ -11,5 +11,5 @@ echo "ncu1 rc=$?"
 $CMD > gpurun_out/plain2.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:force_step -s 3 -c 1 -o gpurun_out/prof $CMD > gpurun_out/ncu2.log 2>&1
 echo "ncu2 rc=$?"
 ./tools/microbench/fp32_pipes > gpurun_out/microbench.txt 2>&1
-timeout 600 python tools/run_reference_configs.py > gpurun_out/reference_configs.json 2> gpurun_out/refcfg.err
+timeout 600 python tests/reference_configs.py > gpurun_out/reference_configs.json 2> gpurun_out/refcfg.err
 timeout 300 python tools/perf_probe.py 1048576 6,3,7,1 cut > gpurun_out/probe_1m.txt 2>&1; cat gpurun_out/probe_1m.txt
