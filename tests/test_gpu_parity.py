@@ -348,6 +348,20 @@ def test_cli_driver_end_to_end(gs, oracle, tmp_path):
     assert line == "Particle 1: (%.14f, %.14f, %.14f)" % tuple(state[1, :3])
 
 
+def test_cli_driver_two_gpus_when_present(gs, oracle, tmp_path):
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    exe = os.path.join(PKG_DIR, "bin", "gravsim")          # one host thread per GPU, as `mpirun -np 2` of mpi.c
+    out = str(tmp_path / "final2.gs")
+    r = subprocess.run([exe, "9000", "8", "3600", "--seed", "5", "--gpus", "2", "--out", out, "--energy", "--quiet"],
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    state, h = gs.state_read(out)
+    ref = oracle.run_sync(gs.ic_reference_uniform(9000, seed=5).astype(np.float64), 3600.0, 8)
+    assert np.abs(state[:, :3] - ref[:, :3]).max() <= 2e-6 * 3e11 and "relative drift" in r.stdout
+
+
 def test_two_gpus_when_present(gs, oracle):
     import threading
     import torch
