@@ -224,7 +224,11 @@ int default_variant(int n, int world, int cut_mode) {
         return kDefaultVariant;
     // small problems: too few (i-tile x j-tile) units to feed 148 SMs -> 512-body i-tiles, 4 CTAs per SM
     const int64_t units6 = ((int64_t)pad6 / world / 1536) * (pad6 / kJTile);
-    if (units6 < 8 * 148) return 10;
+    if (units6 < 8 * 148) {
+        // tiny problems: even 512-body i-tiles leave SMs idle -> 256-body i-tiles (R=2 x 128 threads)
+        const int64_t units10 = ((int64_t)pad6 / world / 512) * (pad6 / kJTile);
+        return units10 < 4 * 148 ? 16 : 10;
+    }
     if (cut_mode != kSoftened) return 3;
     const double cost6 = (double)pad6 * pad6, cost3 = (double)pad3 * pad3 / 0.98;
     return cost6 <= cost3 ? 6 : 3;

@@ -15,7 +15,7 @@ enum CutMode : int { kSoftened = 0,        // eps > 0
 
 // Kernel variants (gs_config.variant / env GRAVSIM_VARIANT): i-bodies per thread R, CTA size, inner
 // unroll, packed f32x2 or scalar arithmetic.  The table lives in gs_kernels.cu (GS_VARIANTS).
-constexpr int kNumVariants = 15;
+constexpr int kNumVariants = 16;
 constexpr int kDefaultVariant = 1;
 constexpr float kPadPosition = 1.0e18f;   // padding bodies: (1e18,1e18,1e18), mu = 0
 struct VariantInfo { int R, threads, unroll, packed, i_tile; };

@@ -127,7 +127,7 @@ def test_fp32_range_sun_and_heavy_body(gs, oracle):
     assert np.isfinite(a).all() and rel_err(a, oracle.accel(b.astype(np.float64))).max() <= ACC_TOL
 
 
-@pytest.mark.parametrize("variant", list(range(1, 16)))
+@pytest.mark.parametrize("variant", list(range(1, 17)))
 def test_every_kernel_variant(gs, oracle, variant):
     b = gs.ic_reference_uniform(3000, seed=variant)
     assert rel_err(gpu_accel(gs, b, variant=variant), oracle.accel(b.astype(np.float64))).max() <= ACC_TOL

@@ -69,7 +69,7 @@ def test_stream_k_partition_covers_every_unit_once(gs, ni, nj, grid):
 
 
 def test_slices_tile_aligned_and_cover(gs):
-    for variant in (1, 3, 5, 6, 7, 10, 11, 12, 13):
+    for variant in (1, 3, 5, 6, 7, 10, 11, 12, 13, 16):
         it, jt = gs.plan_tiles(variant)
         for n, w in ((3, 1), (8, 4), (4096, 4), (65536, 1), (1048576, 8), (1000003, 2)):
             prev_end = 0
