@@ -23,6 +23,7 @@ FLAG_NO_UNIFORM_MASS = 4
 FLAG_OVERLAP = 8
 FLAG_NCCL_EXCHANGE = 16
 FLAG_COMPENSATED = 32
+FLAG_SYMMETRIC = 64
 NCCL_ID_BYTES = 128
 
 # every symbol include/gravsim.h declares (checked by the CPU tests)

@@ -5,6 +5,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <new>
+#include <vector>
 #include <unistd.h>
 
 #include "../../include/gravsim.h"
@@ -12,6 +13,11 @@
 #include "gs_nccl_dyn.h"
 
 using namespace gs;
+
+namespace gs {
+void build_sym_plan(int ni, int nj_total, int diag, int grid, int cost_plain, int cost_sym, std::vector<SymCta>& ctas,
+                    std::vector<int2>& rows);
+}
 
 struct gs_ctx {
     gs_config cfg;
@@ -66,6 +72,13 @@ struct gs_ctx {
     float4* h_snap[2] = {nullptr, nullptr};
     cudaEvent_t ev_snap_ready[2] = {nullptr, nullptr}, ev_snap_done[2] = {nullptr, nullptr};
     bool buf_copy_pending[2] = {false, false};   // pos[b] is still being read by a snapshot copy
+    // pair-symmetric pass (GS_FLAG_SYMMETRIC, one GPU)
+    bool symmetric = false;
+    int sym_grid = 0, sym_regs = 0;
+    SymCta* d_sym_ctas = nullptr;
+    int2* d_sym_rows = nullptr;
+    float* d_accj = nullptr;
+    float4* sym_partial = nullptr;
     int buf_copy_event[2] = {0, 0};
 };
 
@@ -165,6 +178,17 @@ int force_pass(gs_ctx* c, int final_mode, float kick, float drift, float4* acc_o
         if ((rc = wait_positions(c)) != GS_OK) return rc;
         p.nj_tiles = p.nj_total; p.j_rot = 0;
         p.acc_in = nullptr; p.acc_out = acc_out; p.final_mode = final_mode;
+        if (c->symmetric) {     // every unordered pair once, both directions; finished by sym_finish_kernel
+            SymParams sp;
+            memset(&sp, 0, sizeof(sp));
+            sp.pos = c->pos[c->cur]; sp.acc_whole = c->acc_stage; sp.partial = c->sym_partial; sp.accj = c->d_accj;
+            sp.ctas = c->d_sym_ctas; sp.n = c->n; sp.ni_tiles = p.ni_tiles; sp.nj_total = p.nj_total;
+            sp.diag = c->i_tile / kJTile; sp.eps2 = c->eps2; sp.cut2 = c->cut2; sp.mu_uniform = c->mu_uniform;
+            GS_CUDA(c, cudaMemsetAsync(c->d_accj, 0, (size_t)c->n_pad * sizeof(float4), c->stream));
+            GS_CUDA(c, launch_sym_force(c->R, c->cut_mode, sp, c->sym_grid, c->stream)); c->launches++;
+            GS_CUDA(c, launch_sym_finish(p, sp, c->d_sym_rows, c->i_tile, &extras, c->stream)); c->launches++;
+            return GS_OK;
+        }
         return run(p, c->split_full);
     }
     const int nj_local = (W > 1) ? c->slice / kJTile : p.nj_total / 2;
@@ -452,6 +476,7 @@ void gs_destroy(gs_ctx* c) {
     cudaFree(c->flags); cudaFree(c->d_comm_err);
     if (c->comm) nccl_api().CommDestroy(c->comm);
     cudaFree(c->pos[0]); cudaFree(c->pos[1]); cudaFree(c->vel); cudaFree(c->vel_full);
+    cudaFree(c->d_sym_ctas); cudaFree(c->d_sym_rows); cudaFree(c->d_accj); cudaFree(c->sym_partial);
     cudaFree(c->pos_lo); cudaFree(c->vel_lo); cudaFree(c->lo_full[0]); cudaFree(c->lo_full[1]);
     cudaFree(c->acc_local); cudaFree(c->acc_stage); cudaFree(c->acc_out); cudaFree(c->partial); cudaFree(c->mass);
     cudaFree(c->d_aos); cudaFree(c->d_energy);
@@ -577,6 +602,28 @@ int gs_create(gs_ctx** out, const gs_config* cfg) {
         (!dmalloc((void**)&c->pos_lo, vel_bytes) || !dmalloc((void**)&c->vel_lo, vel_bytes) ||
          (!c->acc_stage && !dmalloc((void**)&c->acc_stage, vel_bytes))))
         return fail(GS_ENOMEM);
+    if ((c->cfg.flags & GS_FLAG_SYMMETRIC) && cfg->world_size == 1 && c->threads == 256 && (c->R == 4 || c->R == 6)) {
+        if (c->cut_mode == kCutoffTracked) c->cut_mode = kCutoff;
+        int ctas = 0;
+        e = sym_kernel_setup(c->R, c->cut_mode, &ctas, &c->sym_regs);
+        if (e != cudaSuccess || ctas < 1) { c->last_cuda_error = (int)e; return fail(GS_ECUDA); }
+        c->sym_grid = c->sm_count * ctas;
+        if (eg && atoi(eg) > 0 && atoi(eg) <= c->sym_grid) c->sym_grid = atoi(eg);
+        std::vector<SymCta> hc;
+        std::vector<int2> hr;
+        int cost_plain = 100, cost_sym = 133;             // issue cycles per unit, relative
+        if (const char* ev = getenv("GRAVSIM_SYM_COST")) cost_sym = atoi(ev);
+        build_sym_plan(c->slice / c->i_tile, c->n_pad / kJTile, c->i_tile / kJTile, c->sym_grid, cost_plain, cost_sym, hc, hr);
+        if (!dmalloc((void**)&c->d_sym_ctas, hc.size() * sizeof(SymCta)) || !dmalloc((void**)&c->d_sym_rows, hr.size() * sizeof(int2)) ||
+            !dmalloc((void**)&c->d_accj, (size_t)c->n_pad * sizeof(float4)) ||
+            !dmalloc((void**)&c->sym_partial, (size_t)c->sym_grid * 2 * c->i_tile * sizeof(float4)) ||
+            (!c->acc_stage && !dmalloc((void**)&c->acc_stage, vel_bytes)))
+            return fail(GS_ENOMEM);
+        if (cudaMemcpy(c->d_sym_ctas, hc.data(), hc.size() * sizeof(SymCta), cudaMemcpyHostToDevice) != cudaSuccess ||
+            cudaMemcpy(c->d_sym_rows, hr.data(), hr.size() * sizeof(int2), cudaMemcpyHostToDevice) != cudaSuccess)
+            return fail(GS_ECUDA);
+        c->symmetric = true;
+    }
     if ((cfg->world_size > 1 || (c->cfg.flags & GS_FLAG_TWO_PASS)) && !dmalloc((void**)&c->acc_local, vel_bytes))
         return fail(GS_ENOMEM);
     if (cudaHostAlloc((void**)&c->h_energy, ((size_t)egrid * 5 + 8) * sizeof(double), cudaHostAllocDefault) !=

@@ -71,6 +71,23 @@ cudaError_t launch_signal_peers(const PeerFlags& f, int world, int my_rank, uint
 cudaError_t launch_wait_flags(const uint32_t* my_flags, int world, int my_rank, uint32_t value,
                               unsigned long long timeout_ns, uint32_t* err, cudaStream_t s);
 
+// ---- pair-symmetric force pass (gs_symmetric.cu; GS_FLAG_SYMMETRIC, one GPU) --------------------------------
+struct SymCta { int row0, k0, count, pad; };   // a persistent CTA's first unit (row, index in the row) and unit count
+struct SymParams {
+    const float4* pos;       // packed pairs, n_pad bodies
+    float4* acc_whole;       // i-side sums of rows handled by a single CTA (float4 per body)
+    float4* partial;         // [grid][2][i_tile]: i-side sums of rows split between CTAs
+    float* accj;             // j-side sums, float4 per body, accumulated with atomics; zero before the launch
+    const SymCta* ctas;      // [grid]
+    int n, ni_tiles, nj_total, diag;   // diag = i_tile / j_tile plain units open every row
+    float eps2, cut2, mu_uniform;
+};
+size_t sym_smem_bytes();
+cudaError_t sym_kernel_setup(int R, int cut_mode, int* ctas_per_sm, int* regs);
+cudaError_t launch_sym_force(int R, int cut_mode, const SymParams& p, int grid, cudaStream_t s);
+cudaError_t launch_sym_finish(const StepParams& p, const SymParams& sp, const int2* rows, int i_tile,
+                              const FinishExtras* extras, cudaStream_t s);
+
 // AoS <-> packed-pair conversion on the device. `aos` is the raw byte image of the reference's
 // 28-byte (f32) or 56-byte (f64) records.  Bodies >= n are padding (mu = 0, at the origin).
 // pos_lo_local / vel_lo_local (nullable): low-order words, i.e. what rounding the record to fp32 dropped.

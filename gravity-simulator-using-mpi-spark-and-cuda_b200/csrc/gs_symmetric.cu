@@ -1,0 +1,336 @@
+// gs_symmetric.cu -- pair-symmetric force pass (GS_FLAG_SYMMETRIC, one GPU): every unordered pair of
+// bodies in different tiles is evaluated ONCE and applied to both bodies (Newton's third law), which the
+// reference's cuda.cu also does (cuda.cu:43-49) -- there with a data race, here without.
+//
+// Why it pays: the kernel is issue-bound.  A (i-body, j-pair) step costs 26 issue cycles for
+// two directed interactions in the row-gather kernel; sharing d, r^2, rsqrt and rinv^3 between the two
+// directions costs 34 for four.  The usual objection -- the j-side sums need a reduction across the 32 lanes
+// that all look at the same j -- is avoided by ROTATING the j-pairs over the lanes: in iteration `it` lane l
+// works on j-pair (it + l) mod 32 of the current 64-pair chunk (and on that pair + 32), so no two lanes of a
+// warp touch the same j at the same time and each lane simply read-modify-writes that pair's running sums in a
+// per-warp shared-memory accumulator array (conflict-free: consecutive lanes, consecutive entries).
+// After a j-tile the eight warps' arrays are added up and sent to global memory with atomic adds
+// (floating-point atomics: the pass is NOT bit-reproducible, which is why it is opt-in).
+//
+// Work: rows of (i-tile x j-tile) units; row I starts with its `diag` = i_tile/j_tile own j-tiles, done as
+// plain (one-directional, all ordered pairs) units, followed by symmetric units for every j-tile after them;
+// j-tiles before them are covered by earlier rows.  Units are handed to the persistent CTAs as contiguous
+// ranges of equal estimated cost (host-side plan, build_sym_plan); i-side sums of a row split between CTAs go
+// through the same partial-sum scratch as the row-gather kernel; sym_finish_kernel adds i-side and j-side sums
+// and finishes (integration or acceleration output).
+#include <vector>
+
+#include "gs_device.cuh"
+
+namespace gs {
+
+constexpr int kSymThreads = 256;
+constexpr int kSymWarps = kSymThreads / 32;
+constexpr size_t kSymTileBytes = (size_t)kJTile * sizeof(float4);
+constexpr size_t kSymAccABytes = (size_t)kSymWarps * (kJTile / 2) * sizeof(float4);
+constexpr size_t kSymAccBBytes = (size_t)kSymWarps * (kJTile / 2) * sizeof(float2);
+constexpr size_t kSymSmemBytes = kStages * kSymTileBytes + 2 * kStages * sizeof(uint64_t) + 64 + kSymAccABytes + kSymAccBBytes;
+
+// One j-tile, both directions.  accA/accB: THIS warp's j-side running sums ({ax0,ax1,ay0,ay1}, {az0,az1} per j-pair).
+template <int R, int CUT, bool UNI>
+__device__ __forceinline__ void sym_tile(const float4* __restrict__ T, float4* __restrict__ accA,
+                                         float2* __restrict__ accB, int lane, const float2 (&nxi)[R],
+                                         const float2 (&nyi)[R], const float2 (&nzi)[R], const float2 (&nmui)[R],
+                                         float2 eps2, float cut2, Acc<R>& out) {
+    float2 ax[R], ay[R], az[R];
+#pragma unroll
+    for (int b = 0; b < R; ++b) ax[b] = ay[b] = az[b] = make_float2(0.f, 0.f);
+    for (int chunk = 0; chunk < kJTile / 128; ++chunk) {       // 64 j-pairs per chunk
+#pragma unroll 1
+        for (int it = 0; it < 32; ++it) {
+            const int p0 = chunk * 64 + ((it + lane) & 31);
+            const int p1 = p0 + 32;
+            float4 JA[2] = {accA[p0], accA[p1]};
+            float2 JB[2] = {accB[p0], accB[p1]};
+            const float4 A[2] = {T[2 * p0], T[2 * p1]};
+            const float4 B[2] = {T[2 * p0 + 1], T[2 * p1 + 1]};
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const float2 xj = make_float2(A[h].x, A[h].y), yj = make_float2(A[h].z, A[h].w);
+                const float2 zj = make_float2(B[h].x, B[h].y), mj = make_float2(B[h].z, B[h].w);
+                float2 jx = make_float2(JA[h].x, JA[h].y), jy = make_float2(JA[h].z, JA[h].w), jz = JB[h];
+#pragma unroll
+                for (int b = 0; b < R; ++b) {
+                    const float2 dx = __fadd2_rn(xj, nxi[b]);
+                    const float2 dy = __fadd2_rn(yj, nyi[b]);
+                    const float2 dz = __fadd2_rn(zj, nzi[b]);
+                    float2 r2 = __ffma2_rn(dx, dx, eps2);
+                    r2 = __ffma2_rn(dy, dy, r2);
+                    r2 = __ffma2_rn(dz, dz, r2);
+                    float2 ri = make_float2(rsqrt_approx(r2.x), rsqrt_approx(r2.y));
+                    if (CUT != kSoftened) {
+                        ri.x = (r2.x >= cut2) ? ri.x : 0.f;
+                        ri.y = (r2.y >= cut2) ? ri.y : 0.f;
+                    }
+                    const float2 ri2 = __fmul2_rn(ri, ri);
+                    const float2 t = __fmul2_rn(ri2, ri);                       // rinv^3, shared by both directions
+                    const float2 s = UNI ? t : __fmul2_rn(mj, t);               // on i:  +mu_j t d
+                    const float2 u = UNI ? t : __fmul2_rn(nmui[b], t);          // on j:  -mu_i t d  (UNI: sign and mu at the flush)
+                    ax[b] = __ffma2_rn(s, dx, ax[b]);
+                    ay[b] = __ffma2_rn(s, dy, ay[b]);
+                    az[b] = __ffma2_rn(s, dz, az[b]);
+                    jx = __ffma2_rn(u, dx, jx);
+                    jy = __ffma2_rn(u, dy, jy);
+                    jz = __ffma2_rn(u, dz, jz);
+                }
+                JA[h] = make_float4(jx.x, jx.y, jy.x, jy.y);
+                JB[h] = jz;
+            }
+            accA[p0] = JA[0]; accA[p1] = JA[1];
+            accB[p0] = JB[0]; accB[p1] = JB[1];
+            __syncwarp();     // next iteration another lane picks these pairs up
+        }
+    }
+#pragma unroll
+    for (int b = 0; b < R; ++b) {
+        out.x[b] += ax[b].x + ax[b].y;
+        out.y[b] += ay[b].x + ay[b].y;
+        out.z[b] += az[b].x + az[b].y;
+    }
+}
+
+template <int R, int MINB, int CUT, bool UNI>
+__global__ void __launch_bounds__(kSymThreads, MINB) sym_force_kernel(const SymParams p) {
+    constexpr int ITILE = kSymThreads * R;
+    constexpr int NP = R / 2;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    float4* tiles = reinterpret_cast<float4*>(smem_raw);
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + kStages * kSymTileBytes);
+    uint64_t* empty = full + kStages;
+    float4* accA_all = reinterpret_cast<float4*>(smem_raw + kStages * kSymTileBytes + 2 * kStages * sizeof(uint64_t) + 64);
+    float2* accB_all = reinterpret_cast<float2*>(reinterpret_cast<unsigned char*>(accA_all) + kSymAccABytes);
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const SymCta me = p.ctas[blockIdx.x];
+    const int nunits = me.count;
+    if (nunits <= 0) return;
+    float4* accA = accA_all + warp * (kJTile / 2);
+    float2* accB = accB_all + warp * (kJTile / 2);
+
+    if (tid == 0) {
+#pragma unroll
+        for (int s = 0; s < kStages; ++s) {
+            mbar_init(&full[s], 1);
+            mbar_init(&empty[s], kSymWarps);
+        }
+        fence_mbar_init();
+    }
+    for (int e = lane; e < kJTile / 2; e += 32) {
+        accA[e] = make_float4(0.f, 0.f, 0.f, 0.f);
+        accB[e] = make_float2(0.f, 0.f);
+    }
+    __syncthreads();
+
+    // producer cursor: the next unit whose j-tile has to be loaded (only thread 0 uses it)
+    int prow = me.row0, pk = me.k0, loaded = 0;
+    auto load_next = [&](int stage) {
+        const int jtile = p.diag * prow + pk;
+        mbar_arrive_expect_tx(&full[stage], (uint32_t)kSymTileBytes);
+        tma_bulk_g2s(tiles + (size_t)stage * kJTile, p.pos + (size_t)jtile * kJTile, (uint32_t)kSymTileBytes, &full[stage]);
+        ++loaded;
+        if (++pk >= p.nj_total - p.diag * prow) { ++prow; pk = 0; }
+    };
+    if (tid == 0)
+        for (int s = 0; s < kStages && s < nunits; ++s) load_next(s);
+
+    const float2 eps2 = make_float2(p.eps2, p.eps2);
+    int row = me.row0, kk = me.k0, k = 0;
+    while (k < nunits) {
+        const int row_units = p.nj_total - p.diag * row;
+        const int seg = min(row_units - kk, nunits - k);
+        const bool whole = (kk == 0) && (seg == row_units);
+
+        float2 nxi[R], nyi[R], nzi[R], nmui[R];
+        Acc<R> acc;
+#pragma unroll
+        for (int q = 0; q < NP; ++q) {
+            const int pair = row * (ITILE / 2) + q * kSymThreads + tid;
+            const float4 A = p.pos[2 * pair], B = p.pos[2 * pair + 1];
+            nxi[2 * q] = make_float2(-A.x, -A.x); nxi[2 * q + 1] = make_float2(-A.y, -A.y);
+            nyi[2 * q] = make_float2(-A.z, -A.z); nyi[2 * q + 1] = make_float2(-A.w, -A.w);
+            nzi[2 * q] = make_float2(-B.x, -B.x); nzi[2 * q + 1] = make_float2(-B.y, -B.y);
+            nmui[2 * q] = make_float2(-B.z, -B.z); nmui[2 * q + 1] = make_float2(-B.w, -B.w);
+        }
+#pragma unroll
+        for (int b = 0; b < R; ++b) acc.x[b] = acc.y[b] = acc.z[b] = 0.f;
+
+        for (int t = 0; t < seg; ++t, ++k, ++kk) {
+            const int stage = k % kStages;
+            if (tid == 0 && k >= kRefillLag && loaded < nunits) {   // refill the stage used kRefillLag units ago
+                const int kr = k - kRefillLag, sr = kr % kStages;
+                mbar_wait(&empty[sr], (uint32_t)((kr / kStages) & 1));
+                load_next(sr);
+            }
+            mbar_wait(&full[stage], (uint32_t)((k / kStages) & 1));
+            const float4* T = tiles + (size_t)stage * kJTile;
+            const bool symmetric = (kk >= p.diag);
+            if (!symmetric) tile_packed<R, (CUT == kSoftened ? kSoftened : kCutoff), UNI, 2>(T, nxi, nyi, nzi, eps2, p.cut2, acc);
+            else sym_tile<R, CUT, UNI>(T, accA, accB, lane, nxi, nyi, nzi, nmui, eps2, p.cut2, acc);
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty[stage]);
+            if (symmetric) {
+                // j-side sums of this tile: add the eight warps' arrays, send them off, clear them
+                __syncthreads();
+                const int jtile = p.diag * row + kk;
+                const float w = UNI ? -p.mu_uniform : 1.f;
+                for (int e = tid; e < kJTile / 2; e += kSymThreads) {
+                    float4 SA = make_float4(0.f, 0.f, 0.f, 0.f);
+                    float2 SB = make_float2(0.f, 0.f);
+#pragma unroll
+                    for (int wv = 0; wv < kSymWarps; ++wv) {
+                        const float4 a = accA_all[wv * (kJTile / 2) + e];
+                        const float2 b = accB_all[wv * (kJTile / 2) + e];
+                        SA.x += a.x; SA.y += a.y; SA.z += a.z; SA.w += a.w; SB.x += b.x; SB.y += b.y;
+                        accA_all[wv * (kJTile / 2) + e] = make_float4(0.f, 0.f, 0.f, 0.f);
+                        accB_all[wv * (kJTile / 2) + e] = make_float2(0.f, 0.f);
+                    }
+                    float* dst = p.accj + 4 * ((size_t)jtile * kJTile + 2 * e);   // bodies 2e, 2e+1 of the tile
+                    atomicAdd(dst + 0, w * SA.x); atomicAdd(dst + 1, w * SA.z); atomicAdd(dst + 2, w * SB.x);
+                    atomicAdd(dst + 4, w * SA.y); atomicAdd(dst + 5, w * SA.w); atomicAdd(dst + 6, w * SB.y);
+                }
+                __syncthreads();
+            }
+        }
+
+        // i-side sums of this row segment
+#pragma unroll
+        for (int q = 0; q < NP; ++q) {
+            const int in_tile = 2 * (q * kSymThreads + tid);
+            const float w = UNI ? p.mu_uniform : 1.f;
+            const float4 a0 = make_float4(w * acc.x[2 * q], w * acc.y[2 * q], w * acc.z[2 * q], 0.f);
+            const float4 a1 = make_float4(w * acc.x[2 * q + 1], w * acc.y[2 * q + 1], w * acc.z[2 * q + 1], 0.f);
+            float4* dst = whole ? p.acc_whole + (size_t)row * ITILE + in_tile
+                                : p.partial + ((size_t)blockIdx.x * 2 + (row == me.row0 ? 0 : 1)) * ITILE + in_tile;
+            dst[0] = a0; dst[1] = a1;
+        }
+        ++row; kk = 0;
+    }
+}
+
+// a_i = (i-side sums: whole row or per-CTA partials in fixed order) + (j-side sums), then integrate / output.
+__global__ void __launch_bounds__(256) sym_finish_kernel(const StepParams p, const SymParams sp, const int2* rows,
+                                                        int ITILE, const FinishExtras ex) {
+    const int pair_local = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pair_local >= sp.ni_tiles * (ITILE / 2)) return;
+    const int row = pair_local / (ITILE / 2);
+    const int q = pair_local - row * (ITILE / 2);
+    const int2 owners = rows[row];
+    float4 a0, a1;
+    if (owners.x == owners.y) {
+        a0 = sp.acc_whole[2 * (size_t)pair_local];
+        a1 = sp.acc_whole[2 * (size_t)pair_local + 1];
+    } else {
+        a0 = make_float4(0.f, 0.f, 0.f, 0.f); a1 = a0;
+        for (int c = owners.x; c <= owners.y; ++c) {
+            const SymCta cta = sp.ctas[c];
+            if (cta.count <= 0) continue;
+            const float4* src = sp.partial + ((size_t)c * 2 + (row == cta.row0 ? 0 : 1)) * ITILE + 2 * q;
+            const float4 s0 = src[0], s1 = src[1];
+            a0.x += s0.x; a0.y += s0.y; a0.z += s0.z;
+            a1.x += s1.x; a1.y += s1.y; a1.z += s1.z;
+        }
+    }
+    const float4 j0 = reinterpret_cast<const float4*>(sp.accj)[2 * (size_t)pair_local];
+    const float4 j1 = reinterpret_cast<const float4*>(sp.accj)[2 * (size_t)pair_local + 1];
+    a0.x += j0.x; a0.y += j0.y; a0.z += j0.z;
+    a1.x += j1.x; a1.y += j1.y; a1.z += j1.z;
+    finish_pair<true>(p, pair_local, a0, a1, &ex);
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------
+// Contiguous unit ranges of equal estimated cost (plain unit = cost_plain, symmetric unit = cost_sym).
+void build_sym_plan(int ni, int nj_total, int diag, int grid, int cost_plain, int cost_sym, std::vector<SymCta>& ctas,
+                    std::vector<int2>& rows) {
+    auto row_units = [&](int I) { return (int64_t)nj_total - (int64_t)diag * I; };
+    auto row_cost = [&](int I) { return (int64_t)diag * cost_plain + (row_units(I) - diag) * cost_sym; };
+    std::vector<int64_t> prefix(ni + 1, 0), uprefix(ni + 1, 0);
+    for (int I = 0; I < ni; ++I) { prefix[I + 1] = prefix[I] + row_cost(I); uprefix[I + 1] = uprefix[I] + row_units(I); }
+    const int64_t W = prefix[ni];
+    // first unit (row, k) whose start cost is >= c*W/grid
+    std::vector<int> brow(grid + 1), bk(grid + 1);
+    int I = 0;
+    for (int c = 0; c <= grid; ++c) {
+        const int64_t B = (c == grid) ? W : (int64_t)(((__int128)W * c) / grid);
+        while (I < ni && prefix[I + 1] <= B) ++I;
+        if (I >= ni) { brow[c] = ni; bk[c] = 0; continue; }
+        const int64_t off = B - prefix[I];
+        int64_t k;
+        if (off <= (int64_t)diag * cost_plain) k = (off + cost_plain - 1) / cost_plain;
+        else k = diag + (off - (int64_t)diag * cost_plain + cost_sym - 1) / cost_sym;
+        if (k >= row_units(I)) { brow[c] = I + 1; bk[c] = 0; } else { brow[c] = I; bk[c] = (int)k; }
+    }
+    ctas.assign(grid, SymCta{0, 0, 0, 0});
+    rows.assign(ni, int2{grid, -1});
+    for (int c = 0; c < grid; ++c) {
+        const int64_t g0 = uprefix[brow[c]] + bk[c], g1 = uprefix[brow[c + 1]] + bk[c + 1];
+        ctas[c].row0 = brow[c]; ctas[c].k0 = bk[c]; ctas[c].count = (int)(g1 - g0);
+        if (g1 <= g0) continue;
+        const int last_row = (bk[c + 1] == 0) ? brow[c + 1] - 1 : brow[c + 1];
+        for (int r = brow[c]; r <= last_row && r < ni; ++r) {
+            if (c < rows[r].x) rows[r].x = c;
+            if (c > rows[r].y) rows[r].y = c;
+        }
+    }
+}
+
+typedef void (*SymKernel)(const SymParams);
+static SymKernel pick_sym(int R, int cut, bool uni) {
+#define GS_SYM(RR, MB)                                                                                          \
+    if (R == RR) {                                                                                              \
+        if (cut == kSoftened) return uni ? (SymKernel)sym_force_kernel<RR, MB, kSoftened, true>                 \
+                                         : (SymKernel)sym_force_kernel<RR, MB, kSoftened, false>;               \
+        return uni ? (SymKernel)sym_force_kernel<RR, MB, kCutoff, true> : (SymKernel)sym_force_kernel<RR, MB, kCutoff, false>; \
+    }
+    GS_SYM(4, 1)
+    GS_SYM(6, 1)
+#undef GS_SYM
+    return nullptr;
+}
+
+size_t sym_smem_bytes() { return kSymSmemBytes; }
+
+cudaError_t sym_kernel_setup(int R, int cut_mode, int* ctas_per_sm, int* regs) {
+    int best = 1 << 30, r = 0;
+    for (int uni = 0; uni < 2; ++uni) {
+        SymKernel k = pick_sym(R, cut_mode, uni != 0);
+        if (!k) return cudaErrorInvalidValue;
+        cudaError_t e = cudaFuncSetAttribute((const void*)k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSymSmemBytes);
+        if (e != cudaSuccess) return e;
+        int n = 0;
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, (const void*)k, kSymThreads, kSymSmemBytes);
+        if (e != cudaSuccess) return e;
+        cudaFuncAttributes fa;
+        e = cudaFuncGetAttributes(&fa, (const void*)k);
+        if (e != cudaSuccess) return e;
+        if (n < best) best = n;
+        if (fa.numRegs > r) r = fa.numRegs;
+    }
+    *ctas_per_sm = best;
+    *regs = r;
+    return cudaSuccess;
+}
+
+cudaError_t launch_sym_force(int R, int cut_mode, const SymParams& p, int grid, cudaStream_t s) {
+    SymKernel k = pick_sym(R, cut_mode, p.mu_uniform != 0.f);
+    if (!k) return cudaErrorInvalidValue;
+    k<<<grid, kSymThreads, kSymSmemBytes, s>>>(p);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_sym_finish(const StepParams& p, const SymParams& sp, const int2* rows, int i_tile,
+                              const FinishExtras* extras, cudaStream_t s) {
+    const int pairs = sp.ni_tiles * (i_tile / 2);
+    FinishExtras none;
+    none.peers.n = 0; none.pos_lo = nullptr; none.vel_lo = nullptr;
+    sym_finish_kernel<<<(pairs + 255) / 256, 256, 0, s>>>(p, sp, rows, i_tile, extras ? *extras : none);
+    return cudaGetLastError();
+}
+
+}  // namespace gs

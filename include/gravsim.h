@@ -71,6 +71,9 @@ typedef struct gs_config {
 #define GS_FLAG_NO_UNIFORM_MASS 4u /* keep the general kernel even when all masses are equal        */
 #define GS_FLAG_OVERLAP    8u   /* multi-GPU: own j-slice first, remote slices after the exchange  */
 #define GS_FLAG_NCCL_EXCHANGE 16u /* multi-GPU: per-step ncclAllGather instead of peer-memory stores */
+#define GS_FLAG_SYMMETRIC  64u   /* one GPU: evaluate every unordered pair once and apply it to both bodies
+                                   (cuda.cu:43-49 without the race); ~1.4x faster, uses floating-point
+                                   atomics, so results are not bit-reproducible between runs           */
 #define GS_FLAG_COMPENSATED 32u /* positions and velocities as hi+lo fp32 pairs: the integration no longer
                                    rounds to the state's fp32 ulp each step (forces stay fp32); f64 records
                                    keep their low-order bits through upload/download                    */

@@ -187,6 +187,28 @@ def test_two_pass_schedule_matches_single_pass(gs, oracle):
         assert np.abs(out[:, :3] - ref[:, :3]).max() <= 2e-6 * 3e11
 
 
+@pytest.mark.parametrize("grid", [0, 1, 5, 37])
+def test_symmetric_pass(gs, oracle, grid, monkeypatch):
+    # GS_FLAG_SYMMETRIC: every unordered pair once, both directions (floating-point atomics: tolerance, not bits)
+    if grid:
+        monkeypatch.setenv("GRAVSIM_GRID", str(grid))
+    for variant in (6, 1):
+        b = gs.ic_reference_uniform(7001, seed=60 + variant)                 # general masses, cutoff rule, padding
+        b[11] = b[5]                                                          # a coincident pair
+        with gs.GravSim(7001, flags=gs.FLAG_SYMMETRIC, variant=variant) as sim:
+            sim.upload(b)
+            a = sim.accel()
+            sim.step(3)
+            out = sim.download()
+        assert np.isfinite(a).all() and rel_err(a, oracle.accel(b.astype(np.float64))).max() <= ACC_TOL
+        ref = oracle.run_sync(b.astype(np.float64), 3600.0, 3)
+        assert np.abs(out[:, :3] - ref[:, :3]).max() <= 2e-6 * 3e11
+        p = gs.ic_plummer(6000, seed=variant)                                 # equal masses, softened
+        ref = oracle.accel_subset(p.astype(np.float64), np.arange(6000), G=1.0, eps=0.02, massfree=True)[0]
+        for flags in (gs.FLAG_SYMMETRIC, gs.FLAG_SYMMETRIC | gs.FLAG_NO_UNIFORM_MASS):
+            assert rel_err(gpu_accel(gs, p, G=1.0, eps=0.02, flags=flags, variant=variant), ref).max() <= 5e-5
+
+
 # ---- integration ------------------------------------------------------------------------------------
 def _traj_err(out, ref):
     pos = np.abs(out[:, :3].astype(np.float64) - ref[:, :3]).max() / np.abs(ref[:, :3]).max()
