@@ -287,6 +287,8 @@ def main():
                 "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": dict(workload_config(world), n_bodies=n, variant=info.variant, grid=info.grid,
                                i_tile=info.i_tile, j_tile=info.j_tile, regs=info.regs_per_thread,
+                               force_pass="pair-symmetric (each unordered pair once, both bodies)" if info.symmetric
+                               else "row gather (each ordered pair)",
                                mass_path="uniform (all masses equal: mass factor hoisted out of the inner loop)"
                                if info.uniform_mass else "general",
                                exchange=("peer-memory stores fused in the integrate epilogue + flags" if info.peer_exchange

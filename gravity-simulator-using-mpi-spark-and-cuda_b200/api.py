@@ -24,6 +24,7 @@ FLAG_OVERLAP = 8
 FLAG_NCCL_EXCHANGE = 16
 FLAG_COMPENSATED = 32
 FLAG_SYMMETRIC = 64
+FLAG_DETERMINISTIC = 128
 NCCL_ID_BYTES = 128
 
 # every symbol include/gravsim.h declares (checked by the CPU tests)
@@ -65,7 +66,7 @@ class GsInfo(C.Structure):
         ("sm_count", C.c_int32), ("grid", C.c_int32), ("i_tile", C.c_int32), ("j_tile", C.c_int32),
         ("stages", C.c_int32), ("variant", C.c_int32), ("regs_per_thread", C.c_int32),
         ("threads", C.c_int32), ("scratch_bytes", C.c_int64), ("peer_exchange", C.c_int32),
-        ("uniform_mass", C.c_int32),
+        ("uniform_mass", C.c_int32), ("symmetric", C.c_int32), ("reserved", C.c_int32),
     ]
 
 

@@ -15,7 +15,7 @@
 using namespace gs;
 
 namespace gs {
-void build_sym_plan(int ni, int nj_total, int diag, int grid, int cost_plain, int cost_sym, std::vector<SymCta>& ctas,
+void build_sym_plan(const SymParams& sp, int grid, int cost_plain, int cost_sym, std::vector<SymCta>& ctas,
                     std::vector<int2>& rows);
 }
 
@@ -61,7 +61,7 @@ struct gs_ctx {
     float4* peer_pos[2][kMaxPeers + 1] = {};   // [buffer][rank]: every rank's pos buffers as seen from this GPU
     uint32_t* flags = nullptr;                 // my flag array: flags[q] = exchanges rank q has completed into my buffers
     uint32_t* peer_flags[kMaxPeers + 1] = {};  // rank q's flag array as seen from this GPU
-    void* ipc_opened[3 * (kMaxPeers + 1)] = {};
+    void* ipc_opened[4 * (kMaxPeers + 1)] = {};
     int n_ipc_opened = 0;
     uint32_t* d_comm_err = nullptr;            // set by the wait kernel on timeout
     uint32_t xstep = 0;                        // exchanges issued so far (same on every rank)
@@ -77,8 +77,11 @@ struct gs_ctx {
     int sym_grid = 0, sym_regs = 0;
     SymCta* d_sym_ctas = nullptr;
     int2* d_sym_rows = nullptr;
-    float* d_accj = nullptr;
+    float* d_accj = nullptr;                    // j-side sums of MY bodies (peers add into it over NVLink)
+    float* peer_accj[kMaxPeers + 1] = {};       // every rank's accj as seen from this GPU
     float4* sym_partial = nullptr;
+    bool want_sym = false, p2p_atomics = false;
+    uint32_t fstep = 0;                         // symmetric passes whose remote atomics were fenced so far
     int buf_copy_event[2] = {0, 0};
 };
 
@@ -107,6 +110,21 @@ int ensure_aos(gs_ctx* c, size_t bytes) {
     GS_CUDA(c, cudaMalloc(&c->d_aos, bytes));
     c->d_aos_bytes = bytes;
     return GS_OK;
+}
+
+// Geometry of the pair-symmetric pass for this rank (see SymParams): own triangle, the next
+// floor((P-1)/2) slices whole, and for even P the opposite slice shared half/half with its owner.
+void fill_sym_geometry(const gs_ctx* c, SymParams* sp) {
+    memset(sp, 0, sizeof(*sp));
+    const int P = c->cfg.world_size, r = c->cfg.rank;
+    sp->n = c->n; sp->i_begin = c->i_begin;
+    sp->ni_tiles = c->slice / c->i_tile;
+    sp->slice_tiles = c->slice / kJTile;
+    sp->diag = c->i_tile / kJTile;
+    sp->rank = r; sp->world = P;
+    sp->full_slices = (P - 1) / 2;
+    sp->half_rows = sp->ni_tiles / 2;
+    sp->half_mode = (P > 1 && P % 2 == 0) ? (r < P / 2 ? 1 : 2) : 0;
 }
 
 // Orders "every rank's bodies of pos[cur] are in this GPU's memory" before whatever is enqueued next on
@@ -178,14 +196,24 @@ int force_pass(gs_ctx* c, int final_mode, float kick, float drift, float4* acc_o
         if ((rc = wait_positions(c)) != GS_OK) return rc;
         p.nj_tiles = p.nj_total; p.j_rot = 0;
         p.acc_in = nullptr; p.acc_out = acc_out; p.final_mode = final_mode;
-        if (c->symmetric) {     // every unordered pair once, both directions; finished by sym_finish_kernel
+        // every unordered pair once, both directions; finished by sym_finish_kernel.  On several GPUs only the
+        // integrating pass (it is collective: peers add into my j-side sums and I into theirs).
+        if (c->symmetric && (W == 1 || final_mode == kFinalIntegrate)) {
             SymParams sp;
-            memset(&sp, 0, sizeof(sp));
-            sp.pos = c->pos[c->cur]; sp.acc_whole = c->acc_stage; sp.partial = c->sym_partial; sp.accj = c->d_accj;
-            sp.ctas = c->d_sym_ctas; sp.n = c->n; sp.ni_tiles = p.ni_tiles; sp.nj_total = p.nj_total;
-            sp.diag = c->i_tile / kJTile; sp.eps2 = c->eps2; sp.cut2 = c->cut2; sp.mu_uniform = c->mu_uniform;
-            GS_CUDA(c, cudaMemsetAsync(c->d_accj, 0, (size_t)c->n_pad * sizeof(float4), c->stream));
+            fill_sym_geometry(c, &sp);
+            sp.pos = c->pos[c->cur]; sp.acc_whole = c->acc_stage; sp.partial = c->sym_partial;
+            for (int q = 0; q < W; ++q) sp.accj[q] = c->peer_accj[q];
+            sp.ctas = c->d_sym_ctas; sp.eps2 = c->eps2; sp.cut2 = c->cut2; sp.mu_uniform = c->mu_uniform;
             GS_CUDA(c, launch_sym_force(c->R, c->cut_mode, sp, c->sym_grid, c->stream)); c->launches++;
+            if (W > 1) {    // my j-side sums are complete once every peer's force kernel has finished
+                PeerFlags f;
+                for (int q = 0; q < W; ++q) f.slot[q] = c->peer_flags[q] + 16 + c->cfg.rank;
+                c->fstep++;
+                GS_CUDA(c, launch_signal_peers(f, W, c->cfg.rank, c->fstep, c->stream));
+                GS_CUDA(c, launch_wait_flags(c->flags + 16, W, c->cfg.rank, c->fstep, c->comm_timeout_ns, c->d_comm_err,
+                                             c->stream));
+                c->launches += 2;
+            }
             GS_CUDA(c, launch_sym_finish(p, sp, c->d_sym_rows, c->i_tile, &extras, c->stream)); c->launches++;
             return GS_OK;
         }
@@ -241,10 +269,11 @@ int sync_velocities(gs_ctx* c) {
 // Measured on B200 at N = 1M (profiles/r1_variant_probe_n1048576.txt): softened -> R=6 x 256 threads (72.0 % general,
 // 78.7 % equal masses), cutoff -> R=8 x 256 threads (65.2 %).  R=6 has a 1536-body i-tile, which pads some
 // N / GPU-count combinations more than the 2048-body tile of R=8 does: charge each its padded work.
-int default_variant(int n, int world, int cut_mode) {
-    int pad6 = 0, pad3 = 0;
+int default_variant(int n, int world, int cut_mode, uint32_t flags) {
+    int pad6 = 0, pad3 = 0, pad1 = 0;
     if (gs_plan_slice(n, world, 0, 6, &pad6, nullptr, nullptr) != GS_OK ||
-        gs_plan_slice(n, world, 0, 3, &pad3, nullptr, nullptr) != GS_OK)
+        gs_plan_slice(n, world, 0, 3, &pad3, nullptr, nullptr) != GS_OK ||
+        gs_plan_slice(n, world, 0, 1, &pad1, nullptr, nullptr) != GS_OK)
         return kDefaultVariant;
     // small problems: too few (i-tile x j-tile) units to feed 148 SMs -> 512-body i-tiles, 4 CTAs per SM
     const int64_t units6 = ((int64_t)pad6 / world / 1536) * (pad6 / kJTile);
@@ -252,6 +281,11 @@ int default_variant(int n, int world, int cut_mode) {
         // tiny problems: even 512-body i-tiles leave SMs idle -> 256-body i-tiles (R=2 x 128 threads)
         const int64_t units10 = ((int64_t)pad6 / world / 512) * (pad6 / kJTile);
         return units10 < 4 * 148 ? 16 : 10;
+    }
+    if (!(flags & GS_FLAG_DETERMINISTIC) && world <= kMaxPeers + 1) {
+        // pair-symmetric pass (R = 6 or 4, 256 threads): R = 6 unless its 1536-body tile pads this N much worse
+        const double cost6 = (double)pad6 * pad6, cost1 = (double)pad1 * pad1 / 0.95;
+        return cost6 <= cost1 ? 6 : 1;
     }
     if (cut_mode != kSoftened) return 3;
     const double cost6 = (double)pad6 * pad6, cost3 = (double)pad3 * pad3 / 0.98;
@@ -265,11 +299,11 @@ int default_variant(int n, int world, int cut_mode) {
 struct PeerBlob {
     long long pid;
     int device, ok;
-    cudaIpcMemHandle_t handle[3];
-    void* raw[3];
-    char pad[256 - 16 - 3 * sizeof(cudaIpcMemHandle_t) - 3 * sizeof(void*)];
+    cudaIpcMemHandle_t handle[4];      // pos[0], pos[1], flags, j-side sums (pair-symmetric pass; may be absent)
+    void* raw[4];
+    char pad[512 - 16 - 4 * sizeof(cudaIpcMemHandle_t) - 4 * sizeof(void*)];
 };
-static_assert(sizeof(PeerBlob) == 256, "PeerBlob is exchanged as 256 raw bytes");
+static_assert(sizeof(PeerBlob) == 512, "PeerBlob is exchanged as 512 raw bytes");
 
 void close_peer_mappings(gs_ctx* c) {
     for (int k = 0; k < c->n_ipc_opened; ++k) cudaIpcCloseMemHandle(c->ipc_opened[k]);
@@ -290,8 +324,9 @@ int setup_peer_exchange(gs_ctx* c) {
     mine.pid = (long long)getpid();
     mine.device = c->device;
     mine.ok = 1;
-    void* ptrs[3] = {c->pos[0], c->pos[1], c->flags};
-    for (int k = 0; k < 3; ++k) {
+    void* ptrs[4] = {c->pos[0], c->pos[1], c->flags, c->d_accj};
+    const int nh = c->d_accj ? 4 : 3;
+    for (int k = 0; k < nh; ++k) {
         mine.raw[k] = ptrs[k];
         if (cudaIpcGetMemHandle(&mine.handle[k], ptrs[k]) != cudaSuccess) { cudaGetLastError(); mine.ok = 0; }
     }
@@ -307,23 +342,26 @@ int setup_peer_exchange(gs_ctx* c) {
             nc.AllGather(d_blobs + me, d_blobs, sizeof(PeerBlob), ncclChar, c->comm, c->stream) != ncclSuccess ||
             cudaMemcpyAsync(h_blobs, d_blobs, sizeof(PeerBlob) * W, cudaMemcpyDeviceToHost, c->stream) != cudaSuccess ||
             cudaStreamSynchronize(c->stream) != cudaSuccess) { rc = GS_ENCCL; break; }
-        int ok = 1;
+        int ok = 1, atomics = 1;
         for (int q = 0; q < W && ok; ++q) ok = h_blobs[q].ok;
         for (int q = 0; q < W && ok; ++q) {
             if (q == me) {
                 c->peer_pos[0][q] = c->pos[0]; c->peer_pos[1][q] = c->pos[1]; c->peer_flags[q] = c->flags;
                 continue;
             }
-            void* mapped[3] = {nullptr, nullptr, nullptr};
+            void* mapped[4] = {nullptr, nullptr, nullptr, nullptr};
+            int native = 0;      // remote atomics over NVLink, needed by the pair-symmetric pass
+            if (cudaDeviceGetP2PAttribute(&native, cudaDevP2PAttrNativeAtomicSupported, c->device, h_blobs[q].device) !=
+                    cudaSuccess || !native) { cudaGetLastError(); atomics = 0; }
             if (h_blobs[q].pid == mine.pid) {        // another thread of this process: plain peer access
                 int can = 0;
                 if (cudaDeviceCanAccessPeer(&can, c->device, h_blobs[q].device) != cudaSuccess || !can) { ok = 0; break; }
                 cudaError_t e = cudaDeviceEnablePeerAccess(h_blobs[q].device, 0);
                 if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) { ok = 0; break; }
                 cudaGetLastError();
-                for (int k = 0; k < 3; ++k) mapped[k] = h_blobs[q].raw[k];
+                for (int k = 0; k < nh; ++k) mapped[k] = h_blobs[q].raw[k];
             } else {                                 // another process: CUDA IPC
-                for (int k = 0; k < 3 && ok; ++k) {
+                for (int k = 0; k < nh && ok; ++k) {
                     if (cudaIpcOpenMemHandle(&mapped[k], h_blobs[q].handle[k], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
                         cudaGetLastError(); ok = 0;
                     } else {
@@ -334,7 +372,9 @@ int setup_peer_exchange(gs_ctx* c) {
             }
             c->peer_pos[0][q] = (float4*)mapped[0]; c->peer_pos[1][q] = (float4*)mapped[1];
             c->peer_flags[q] = (uint32_t*)mapped[2];
+            c->peer_accj[q] = (float*)mapped[3];
         }
+        if (ok) ok = atomics ? 2 : 1;      // min over ranks: 0 no peer access, 1 stores only, 2 stores + atomics
         // unanimous decision
         if (cudaMemcpyAsync(d_ok, &ok, sizeof(int), cudaMemcpyHostToDevice, c->stream) != cudaSuccess ||
             nc.AllReduce(d_ok, d_ok, 1, ncclInt, ncclMin, c->comm, c->stream) != ncclSuccess ||
@@ -347,6 +387,7 @@ int setup_peer_exchange(gs_ctx* c) {
     if (all_ok) {
         if (!c->acc_stage) GS_CUDA(c, cudaMalloc((void**)&c->acc_stage, (size_t)c->slice * sizeof(float4)));
         c->p2p = true;
+        c->p2p_atomics = (all_ok == 2);
     } else {
         close_peer_mappings(c);
     }
@@ -362,6 +403,35 @@ void peer_exchange_goodbye(gs_ctx* c) {
     launch_signal_peers(f, c->cfg.world_size, c->cfg.rank, c->xstep, c->stream);
     launch_wait_flags(c->flags, c->cfg.world_size, c->cfg.rank, c->xstep, 5000000000ull, c->d_comm_err, c->stream);
     cudaStreamSynchronize(c->stream);
+}
+
+// Second half of the pair-symmetric set-up, once it is known whether peers can be reached with atomics.
+int setup_symmetric(gs_ctx* c) {
+    if (!c->want_sym) return GS_OK;
+    if (c->cfg.world_size > 1 && !(c->p2p && c->p2p_atomics)) return GS_OK;     // stay on the row-gather kernel
+    if (c->cut_mode == kCutoffTracked) c->cut_mode = kCutoff;
+    int ctas = 0;
+    cudaError_t e = sym_kernel_setup(c->R, c->cut_mode, &ctas, &c->sym_regs);
+    if (e != cudaSuccess || ctas < 1) { c->last_cuda_error = (int)e; return GS_ECUDA; }
+    c->sym_grid = c->sm_count * ctas;
+    const char* eg = getenv("GRAVSIM_GRID");
+    if (eg && atoi(eg) > 0 && atoi(eg) <= c->sym_grid) c->sym_grid = atoi(eg);
+    SymParams geo;
+    fill_sym_geometry(c, &geo);
+    std::vector<SymCta> hc;
+    std::vector<int2> hr;
+    int cost_plain = 100, cost_sym = 133;                 // issue cycles per unit, relative (34 vs 26 per j-pair and i-body)
+    if (const char* ev = getenv("GRAVSIM_SYM_COST")) cost_sym = atoi(ev);
+    build_sym_plan(geo, c->sym_grid, cost_plain, cost_sym, hc, hr);
+    const size_t slice_bytes = (size_t)c->slice * sizeof(float4);
+    GS_CUDA(c, cudaMalloc((void**)&c->d_sym_ctas, hc.size() * sizeof(SymCta)));
+    GS_CUDA(c, cudaMalloc((void**)&c->d_sym_rows, hr.size() * sizeof(int2)));
+    GS_CUDA(c, cudaMalloc((void**)&c->sym_partial, (size_t)c->sym_grid * 2 * c->i_tile * sizeof(float4)));
+    if (!c->acc_stage) GS_CUDA(c, cudaMalloc((void**)&c->acc_stage, slice_bytes));
+    GS_CUDA(c, cudaMemcpy(c->d_sym_ctas, hc.data(), hc.size() * sizeof(SymCta), cudaMemcpyHostToDevice));
+    GS_CUDA(c, cudaMemcpy(c->d_sym_rows, hr.data(), hr.size() * sizeof(int2), cudaMemcpyHostToDevice));
+    c->symmetric = true;
+    return GS_OK;
 }
 
 int set_device(gs_ctx* c) {
@@ -532,7 +602,7 @@ int gs_create(gs_ctx** out, const gs_config* cfg) {
     c->variant = cfg->variant;
     if (c->variant == 0) {
         const char* ev = getenv("GRAVSIM_VARIANT");
-        c->variant = ev ? atoi(ev) : default_variant(cfg->n, cfg->world_size, c->cut_mode);
+        c->variant = ev ? atoi(ev) : default_variant(cfg->n, cfg->world_size, c->cut_mode, c->cfg.flags);
     }
     VariantInfo vi;
     if (!variant_info(c->variant, &vi)) return fail(GS_EINVAL);
@@ -602,27 +672,13 @@ int gs_create(gs_ctx** out, const gs_config* cfg) {
         (!dmalloc((void**)&c->pos_lo, vel_bytes) || !dmalloc((void**)&c->vel_lo, vel_bytes) ||
          (!c->acc_stage && !dmalloc((void**)&c->acc_stage, vel_bytes))))
         return fail(GS_ENOMEM);
-    if ((c->cfg.flags & GS_FLAG_SYMMETRIC) && cfg->world_size == 1 && c->threads == 256 && (c->R == 4 || c->R == 6)) {
-        if (c->cut_mode == kCutoffTracked) c->cut_mode = kCutoff;
-        int ctas = 0;
-        e = sym_kernel_setup(c->R, c->cut_mode, &ctas, &c->sym_regs);
-        if (e != cudaSuccess || ctas < 1) { c->last_cuda_error = (int)e; return fail(GS_ECUDA); }
-        c->sym_grid = c->sm_count * ctas;
-        if (eg && atoi(eg) > 0 && atoi(eg) <= c->sym_grid) c->sym_grid = atoi(eg);
-        std::vector<SymCta> hc;
-        std::vector<int2> hr;
-        int cost_plain = 100, cost_sym = 133;             // issue cycles per unit, relative
-        if (const char* ev = getenv("GRAVSIM_SYM_COST")) cost_sym = atoi(ev);
-        build_sym_plan(c->slice / c->i_tile, c->n_pad / kJTile, c->i_tile / kJTile, c->sym_grid, cost_plain, cost_sym, hc, hr);
-        if (!dmalloc((void**)&c->d_sym_ctas, hc.size() * sizeof(SymCta)) || !dmalloc((void**)&c->d_sym_rows, hr.size() * sizeof(int2)) ||
-            !dmalloc((void**)&c->d_accj, (size_t)c->n_pad * sizeof(float4)) ||
-            !dmalloc((void**)&c->sym_partial, (size_t)c->sym_grid * 2 * c->i_tile * sizeof(float4)) ||
-            (!c->acc_stage && !dmalloc((void**)&c->acc_stage, vel_bytes)))
-            return fail(GS_ENOMEM);
-        if (cudaMemcpy(c->d_sym_ctas, hc.data(), hc.size() * sizeof(SymCta), cudaMemcpyHostToDevice) != cudaSuccess ||
-            cudaMemcpy(c->d_sym_rows, hr.data(), hr.size() * sizeof(int2), cudaMemcpyHostToDevice) != cudaSuccess)
-            return fail(GS_ECUDA);
-        c->symmetric = true;
+    // pair-symmetric pass: wanted unless the caller asks for bit-reproducible sums; needs a 256-thread R=4/6 variant
+    c->want_sym = !(c->cfg.flags & GS_FLAG_DETERMINISTIC) && c->threads == 256 && (c->R == 4 || c->R == 6) &&
+                  cfg->world_size <= kMaxPeers + 1;
+    if (c->want_sym) {      // allocated now so that setup_peer_exchange() can publish it to the peers
+        if (!dmalloc((void**)&c->d_accj, vel_bytes)) return fail(GS_ENOMEM);
+        if (cudaMemset(c->d_accj, 0, vel_bytes) != cudaSuccess) return fail(GS_ECUDA);
+        c->peer_accj[cfg->rank] = c->d_accj;
     }
     if ((cfg->world_size > 1 || (c->cfg.flags & GS_FLAG_TWO_PASS)) && !dmalloc((void**)&c->acc_local, vel_bytes))
         return fail(GS_ENOMEM);
@@ -648,6 +704,7 @@ int gs_create(gs_ctx** out, const gs_config* cfg) {
         if (nc.CommInitRank(&c->comm, cfg->world_size, id, cfg->rank) != ncclSuccess) return fail(GS_ENCCL);
         if ((rc = setup_peer_exchange(c)) != GS_OK) return fail(rc);
     }
+    if ((rc = setup_symmetric(c)) != GS_OK) return fail(rc);
     *out = c;
     return GS_OK;
 }
@@ -948,6 +1005,7 @@ int gs_get_info(const gs_ctx* c, gs_info* info) {
     info->scratch_bytes = (int64_t)c->partial_bytes;
     info->peer_exchange = c->p2p ? 1 : 0;
     info->uniform_mass = c->mu_uniform != 0.f ? 1 : 0;
+    info->symmetric = c->symmetric ? 1 : 0;
     return GS_OK;
 }
 

@@ -74,14 +74,43 @@ cudaError_t launch_wait_flags(const uint32_t* my_flags, int world, int my_rank, 
 // ---- pair-symmetric force pass (gs_symmetric.cu; GS_FLAG_SYMMETRIC, one GPU) --------------------------------
 struct SymCta { int row0, k0, count, pad; };   // a persistent CTA's first unit (row, index in the row) and unit count
 struct SymParams {
-    const float4* pos;       // packed pairs, n_pad bodies
-    float4* acc_whole;       // i-side sums of rows handled by a single CTA (float4 per body)
+    const float4* pos;       // packed pairs, n_pad bodies (every rank's)
+    float4* acc_whole;       // i-side sums of rows handled by a single CTA (float4 per local body)
     float4* partial;         // [grid][2][i_tile]: i-side sums of rows split between CTAs
-    float* accj;             // j-side sums, float4 per body, accumulated with atomics; zero before the launch
+    float* accj[kMaxPeers + 1];   // per rank: j-side sums of ITS bodies (float4 per local body); mine is local memory,
+                                  // the others are NVLink peer memory; accumulated with atomics, zero before the pass
     const SymCta* ctas;      // [grid]
-    int n, ni_tiles, nj_total, diag;   // diag = i_tile / j_tile plain units open every row
+    int n, i_begin;          // real bodies; first body of this rank's slice
+    int ni_tiles;            // rows = i-tiles of this rank's slice
+    int slice_tiles;         // j-tiles per rank slice (= ni_tiles * diag)
+    int diag;                // i_tile / j_tile: that many plain units open every row
+    int rank, world;
+    int full_slices;         // floor((world-1)/2): slices rank+1 .. rank+full_slices (mod world) are taken whole
+    int half_mode, half_rows;   // world even: the opposite slice is shared with its owner --
+                                //   1: my rows < half_rows take all of its tiles; 2: all my rows take its tiles from
+                                //   half_rows*diag on; 0: world odd or 1
     float eps2, cut2, mu_uniform;
 };
+// Units of row I of `rank`: own tiles from the row's own on, then the whole slices, then the shared opposite slice.
+GS_HD int sym_row_units(const SymParams& p, int row) {
+    int n = p.slice_tiles - p.diag * row + p.full_slices * p.slice_tiles;
+    if (p.half_mode == 1) n += (row < p.half_rows) ? p.slice_tiles : 0;
+    else if (p.half_mode == 2) n += p.slice_tiles - p.half_rows * p.diag;
+    return n;
+}
+// Global j-tile of unit k of row `row`.
+GS_HD int sym_unit_tile(const SymParams& p, int row, int k) {
+    const int own = p.slice_tiles - p.diag * row;
+    if (k < own) return p.rank * p.slice_tiles + p.diag * row + k;
+    k -= own;
+    if (k < p.full_slices * p.slice_tiles) {
+        const int d = k / p.slice_tiles + 1;
+        return ((p.rank + d) % p.world) * p.slice_tiles + (k - (d - 1) * p.slice_tiles);
+    }
+    k -= p.full_slices * p.slice_tiles;
+    const int opposite = (p.rank + p.world / 2) % p.world;
+    return opposite * p.slice_tiles + (p.half_mode == 2 ? p.half_rows * p.diag : 0) + k;
+}
 size_t sym_smem_bytes();
 cudaError_t sym_kernel_setup(int R, int cut_mode, int* ctas_per_sm, int* regs);
 cudaError_t launch_sym_force(int R, int cut_mode, const SymParams& p, int grid, cudaStream_t s);

@@ -129,11 +129,11 @@ __global__ void __launch_bounds__(kSymThreads, MINB) sym_force_kernel(const SymP
     // producer cursor: the next unit whose j-tile has to be loaded (only thread 0 uses it)
     int prow = me.row0, pk = me.k0, loaded = 0;
     auto load_next = [&](int stage) {
-        const int jtile = p.diag * prow + pk;
+        const int jtile = sym_unit_tile(p, prow, pk);
         mbar_arrive_expect_tx(&full[stage], (uint32_t)kSymTileBytes);
         tma_bulk_g2s(tiles + (size_t)stage * kJTile, p.pos + (size_t)jtile * kJTile, (uint32_t)kSymTileBytes, &full[stage]);
         ++loaded;
-        if (++pk >= p.nj_total - p.diag * prow) { ++prow; pk = 0; }
+        if (++pk >= sym_row_units(p, prow)) { ++prow; pk = 0; }
     };
     if (tid == 0)
         for (int s = 0; s < kStages && s < nunits; ++s) load_next(s);
@@ -141,7 +141,7 @@ __global__ void __launch_bounds__(kSymThreads, MINB) sym_force_kernel(const SymP
     const float2 eps2 = make_float2(p.eps2, p.eps2);
     int row = me.row0, kk = me.k0, k = 0;
     while (k < nunits) {
-        const int row_units = p.nj_total - p.diag * row;
+        const int row_units = sym_row_units(p, row);
         const int seg = min(row_units - kk, nunits - k);
         const bool whole = (kk == 0) && (seg == row_units);
 
@@ -149,7 +149,7 @@ __global__ void __launch_bounds__(kSymThreads, MINB) sym_force_kernel(const SymP
         Acc<R> acc;
 #pragma unroll
         for (int q = 0; q < NP; ++q) {
-            const int pair = row * (ITILE / 2) + q * kSymThreads + tid;
+            const int pair = (p.i_begin >> 1) + row * (ITILE / 2) + q * kSymThreads + tid;
             const float4 A = p.pos[2 * pair], B = p.pos[2 * pair + 1];
             nxi[2 * q] = make_float2(-A.x, -A.x); nxi[2 * q + 1] = make_float2(-A.y, -A.y);
             nyi[2 * q] = make_float2(-A.z, -A.z); nyi[2 * q + 1] = make_float2(-A.w, -A.w);
@@ -176,7 +176,9 @@ __global__ void __launch_bounds__(kSymThreads, MINB) sym_force_kernel(const SymP
             if (symmetric) {
                 // j-side sums of this tile: add the eight warps' arrays, send them off, clear them
                 __syncthreads();
-                const int jtile = p.diag * row + kk;
+                const int jtile = sym_unit_tile(p, row, kk);
+                const int owner = jtile / p.slice_tiles;                   // whose bodies these are: local or NVLink peer memory
+                float* const jbase = p.accj[owner] + 4 * (size_t)(jtile - owner * p.slice_tiles) * kJTile;
                 const float w = UNI ? -p.mu_uniform : 1.f;
                 for (int e = tid; e < kJTile / 2; e += kSymThreads) {
                     float4 SA = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -189,7 +191,7 @@ __global__ void __launch_bounds__(kSymThreads, MINB) sym_force_kernel(const SymP
                         accA_all[wv * (kJTile / 2) + e] = make_float4(0.f, 0.f, 0.f, 0.f);
                         accB_all[wv * (kJTile / 2) + e] = make_float2(0.f, 0.f);
                     }
-                    float* dst = p.accj + 4 * ((size_t)jtile * kJTile + 2 * e);   // bodies 2e, 2e+1 of the tile
+                    float* dst = jbase + 4 * (2 * e);                          // bodies 2e, 2e+1 of the tile
                     atomicAdd(dst + 0, w * SA.x); atomicAdd(dst + 1, w * SA.z); atomicAdd(dst + 2, w * SB.x);
                     atomicAdd(dst + 4, w * SA.y); atomicAdd(dst + 5, w * SA.w); atomicAdd(dst + 6, w * SB.y);
                 }
@@ -235,8 +237,10 @@ __global__ void __launch_bounds__(256) sym_finish_kernel(const StepParams p, con
             a1.x += s1.x; a1.y += s1.y; a1.z += s1.z;
         }
     }
-    const float4 j0 = reinterpret_cast<const float4*>(sp.accj)[2 * (size_t)pair_local];
-    const float4 j1 = reinterpret_cast<const float4*>(sp.accj)[2 * (size_t)pair_local + 1];
+    float4* mine = reinterpret_cast<float4*>(sp.accj[sp.rank]);
+    const float4 j0 = mine[2 * (size_t)pair_local], j1 = mine[2 * (size_t)pair_local + 1];
+    mine[2 * (size_t)pair_local] = make_float4(0.f, 0.f, 0.f, 0.f);        // ready for the next pass
+    mine[2 * (size_t)pair_local + 1] = make_float4(0.f, 0.f, 0.f, 0.f);
     a0.x += j0.x; a0.y += j0.y; a0.z += j0.z;
     a1.x += j1.x; a1.y += j1.y; a1.z += j1.z;
     finish_pair<true>(p, pair_local, a0, a1, &ex);
@@ -245,10 +249,12 @@ __global__ void __launch_bounds__(256) sym_finish_kernel(const StepParams p, con
 // ------------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------------
-// Contiguous unit ranges of equal estimated cost (plain unit = cost_plain, symmetric unit = cost_sym).
-void build_sym_plan(int ni, int nj_total, int diag, int grid, int cost_plain, int cost_sym, std::vector<SymCta>& ctas,
+// Contiguous unit ranges of equal estimated cost (plain unit = cost_plain, symmetric unit = cost_sym); only the
+// geometry fields of `sp` are read.
+void build_sym_plan(const SymParams& sp, int grid, int cost_plain, int cost_sym, std::vector<SymCta>& ctas,
                     std::vector<int2>& rows) {
-    auto row_units = [&](int I) { return (int64_t)nj_total - (int64_t)diag * I; };
+    const int ni = sp.ni_tiles, diag = sp.diag;
+    auto row_units = [&](int I) { return (int64_t)sym_row_units(sp, I); };
     auto row_cost = [&](int I) { return (int64_t)diag * cost_plain + (row_units(I) - diag) * cost_sym; };
     std::vector<int64_t> prefix(ni + 1, 0), uprefix(ni + 1, 0);
     for (int I = 0; I < ni; ++I) { prefix[I + 1] = prefix[I] + row_cost(I); uprefix[I + 1] = uprefix[I] + row_units(I); }

@@ -71,9 +71,11 @@ typedef struct gs_config {
 #define GS_FLAG_NO_UNIFORM_MASS 4u /* keep the general kernel even when all masses are equal        */
 #define GS_FLAG_OVERLAP    8u   /* multi-GPU: own j-slice first, remote slices after the exchange  */
 #define GS_FLAG_NCCL_EXCHANGE 16u /* multi-GPU: per-step ncclAllGather instead of peer-memory stores */
-#define GS_FLAG_SYMMETRIC  64u   /* one GPU: evaluate every unordered pair once and apply it to both bodies
-                                   (cuda.cu:43-49 without the race); ~1.4x faster, uses floating-point
-                                   atomics, so results are not bit-reproducible between runs           */
+#define GS_FLAG_SYMMETRIC  64u   /* (default behaviour; kept for callers that set it) pair-symmetric force pass   */
+#define GS_FLAG_DETERMINISTIC 128u /* bit-reproducible sums: use the row-gather kernel instead of the default
+                                   pair-symmetric pass (every unordered pair once, applied to both bodies as
+                                   cuda.cu:43-49 does -- ~1.3x faster, but its floating-point atomics make the
+                                   last bits depend on timing)                                             */
 #define GS_FLAG_COMPENSATED 32u /* positions and velocities as hi+lo fp32 pairs: the integration no longer
                                    rounds to the state's fp32 ulp each step (forces stay fp32); f64 records
                                    keep their low-order bits through upload/download                    */
@@ -89,6 +91,8 @@ typedef struct gs_info {
     int64_t scratch_bytes;        /* device scratch for split-tile partial sums                  */
     int32_t peer_exchange;        /* 1: positions travel by peer-memory stores; 0: ncclAllGather  */
     int32_t uniform_mass;         /* 1: hoisted-mass kernel in use (all masses equal)            */
+    int32_t symmetric;            /* 1: pair-symmetric force pass in use                         */
+    int32_t reserved;
 } gs_info;
 
 /* ---- life cycle -------------------------------------------------------------------------- */

@@ -11,6 +11,7 @@ from conftest import GOLDEN_DIR, G_SI, PKG_DIR, rel_err
 
 pytestmark = pytest.mark.gpu
 
+DET = 128               # gs.FLAG_DETERMINISTIC: the row-gather kernel (the default is the pair-symmetric pass)
 ACC_TOL = 1e-5          # per-body |a_gpu - a_ref| / |a_ref|, fp32 (BASELINE.json north_star)
 
 
@@ -103,20 +104,20 @@ def test_both_cutoff_implementations(gs, oracle, cutmode, monkeypatch):
     # pass that tracks the smallest r^2 and redoes the rare tiles exactly (picked by problem size)
     monkeypatch.setenv("GRAVSIM_CUTMODE", cutmode)
     g = golden("coincident3.npz")
-    assert rel_err(gpu_accel(gs, g["bodies"].astype(np.float32)), g["accel"]).max() <= ACC_TOL
+    assert rel_err(gpu_accel(gs, g["bodies"].astype(np.float32), flags=DET), g["accel"]).max() <= ACC_TOL
     tiny = np.array([[1e-11, 0, 0, 0, 0, 0, 1e3], [5e-11, 0, 0, 0, 0, 0, 2e3], [1.0, 0, 0, 0, 0, 0, 3e3],
                      [0, 2.0, 0, 0, 0, 0, 0.0]], dtype=np.float32)
     ref = oracle.accel_subset(tiny.astype(np.float64), np.arange(4), massfree=True)[0]
-    a = gpu_accel(gs, tiny)
+    a = gpu_accel(gs, tiny, flags=DET)
     assert np.isfinite(a).all() and rel_err(a, ref).max() <= ACC_TOL
     for variant in (0, 1, 6, 10):
         b = gs.ic_reference_uniform(4100, seed=50 + variant)
         b[7] = b[3]                                        # a coincident pair in the middle of a tile
-        a = gpu_accel(gs, b, variant=variant)
+        a = gpu_accel(gs, b, variant=variant, flags=DET)
         assert np.isfinite(a).all() and rel_err(a, oracle.accel(b.astype(np.float64))).max() <= ACC_TOL
     p = gs.ic_plummer(3000, seed=1)                        # equal masses + eps == 0: hoisted-mass kernel, cutoff rule
     ref = oracle.accel_subset(p.astype(np.float64), np.arange(3000), G=1.0, eps=0.0, massfree=True)[0]
-    assert rel_err(gpu_accel(gs, p, G=1.0), ref).max() <= 5e-5
+    assert rel_err(gpu_accel(gs, p, G=1.0, flags=DET), ref).max() <= 5e-5
 
 
 def test_fp32_range_sun_and_heavy_body(gs, oracle):
@@ -130,11 +131,11 @@ def test_fp32_range_sun_and_heavy_body(gs, oracle):
 @pytest.mark.parametrize("variant", list(range(1, 17)))
 def test_every_kernel_variant(gs, oracle, variant):
     b = gs.ic_reference_uniform(3000, seed=variant)
-    assert rel_err(gpu_accel(gs, b, variant=variant), oracle.accel(b.astype(np.float64))).max() <= ACC_TOL
+    assert rel_err(gpu_accel(gs, b, variant=variant, flags=DET), oracle.accel(b.astype(np.float64))).max() <= ACC_TOL
     p = gs.ic_plummer(3000, seed=variant)
     ref = oracle.accel_subset(p.astype(np.float64), np.arange(3000), G=1.0, eps=0.05, massfree=True)[0]
-    assert rel_err(gpu_accel(gs, p, G=1.0, eps=0.05, variant=variant), ref).max() <= 5e-5     # hoisted uniform mass
-    assert rel_err(gpu_accel(gs, p, G=1.0, eps=0.05, variant=variant, flags=gs.FLAG_NO_UNIFORM_MASS), ref).max() <= 5e-5
+    assert rel_err(gpu_accel(gs, p, G=1.0, eps=0.05, variant=variant, flags=DET), ref).max() <= 5e-5     # hoisted uniform mass
+    assert rel_err(gpu_accel(gs, p, G=1.0, eps=0.05, variant=variant, flags=DET | gs.FLAG_NO_UNIFORM_MASS), ref).max() <= 5e-5
 
 
 def test_uniform_mass_path_equals_general_path(gs, oracle):
@@ -144,12 +145,12 @@ def test_uniform_mass_path_equals_general_path(gs, oracle):
     p = gs.ic_plummer(n, seed=3)
     for eps, G in ((0.02, 1.0), (0.0, 1.0)):
         ref = oracle.accel_subset(p.astype(np.float64), np.arange(n), G=G, eps=eps, massfree=True)[0]
-        a_uni = gpu_accel(gs, p, G=G, eps=eps)
-        a_gen = gpu_accel(gs, p, G=G, eps=eps, flags=gs.FLAG_NO_UNIFORM_MASS)
+        a_uni = gpu_accel(gs, p, G=G, eps=eps, flags=DET)
+        a_gen = gpu_accel(gs, p, G=G, eps=eps, flags=DET | gs.FLAG_NO_UNIFORM_MASS)
         assert rel_err(a_uni, ref).max() <= 5e-5 and rel_err(a_gen, ref).max() <= 5e-5
         assert rel_err(a_uni, a_gen.astype(np.float64)).max() <= 5e-6
     ref = oracle.run_sync(p.astype(np.float64), 1.0 / 64, 5, G=1.0, eps=0.02)
-    for flags in (0, gs.FLAG_NO_UNIFORM_MASS, gs.FLAG_TWO_PASS):
+    for flags in (0, DET, DET | gs.FLAG_NO_UNIFORM_MASS, gs.FLAG_TWO_PASS):
         with gs.GravSim(n, dt=1.0 / 64, G=1.0, eps=0.02, flags=flags) as sim:
             sim.upload(p)
             sim.step(5)
@@ -162,7 +163,7 @@ def test_stream_k_split_tiles(gs, oracle, grid, monkeypatch):
     # force odd persistent-grid sizes so i-tiles are split across CTAs and finished by the fix-up kernel
     monkeypatch.setenv("GRAVSIM_GRID", str(grid))
     b = gs.ic_reference_uniform(5000, seed=grid)
-    with gs.GravSim(5000) as sim:
+    with gs.GravSim(5000, flags=DET) as sim:         # the row-gather kernel's partition
         assert sim.info.grid == grid
         sim.upload(b)
         a = sim.accel()
@@ -323,7 +324,7 @@ def test_trajectory_recording(gs):
 # ---- boundary behaviour -------------------------------------------------------------------------------
 def test_round_trip_accel_is_pure_and_deterministic(gs):
     b = gs.ic_reference_uniform(2500, seed=9)
-    with gs.GravSim(2500) as sim:
+    with gs.GravSim(2500, flags=DET) as sim:
         sim.upload(b)
         assert np.array_equal(sim.download(), b)                    # f32 records round-trip bit-exactly
         a1 = sim.accel()
@@ -393,7 +394,7 @@ def test_two_gpus_when_present(gs, oracle):
     b = gs.ic_reference_uniform(n, seed=31)
     ref = oracle.run_sync(b.astype(np.float64), 3600.0, 6)
     # peer-memory exchange (default), with the two-pass overlap schedule, and the NCCL all-gather fallback
-    for flags in (0, gs.FLAG_OVERLAP, gs.FLAG_NCCL_EXCHANGE, gs.FLAG_NCCL_EXCHANGE | gs.FLAG_OVERLAP, gs.FLAG_COMPENSATED):
+    for flags in (0, DET, gs.FLAG_OVERLAP, gs.FLAG_NCCL_EXCHANGE, gs.FLAG_NCCL_EXCHANGE | gs.FLAG_OVERLAP, gs.FLAG_COMPENSATED):
         uid = gs.nccl_unique_id()
         res, errs = [None, None], []
 

@@ -28,7 +28,7 @@ def probe(n, variant, eps, steps=4, grid=None, flags=0):
         dt = (time.perf_counter() - t0) / steps
         info = sim.info
     rate = n * (n - 1.0) / dt
-    print(f"N={n:8d} variant={variant:2d} thr={info.threads} itile={info.i_tile} mass={'general' if (flags & 4 or eps == 0) else 'uniform'}{' SYM' if flags & 64 else ''} mode={'soft' if eps > 0 else 'cut '} grid={info.grid} regs={info.regs_per_thread} "
+    print(f"N={n:8d} variant={variant:2d} thr={info.threads} itile={info.i_tile} mass={'general' if (flags & 4 or eps == 0) else 'uniform'}{' SYM' if info.symmetric else ''} mode={'soft' if eps > 0 else 'cut '} grid={info.grid} regs={info.regs_per_thread} "
           f"{dt * 1e3:9.3f} ms/step  {rate:.3e} int/s  {rate * 20 / PEAK * 100:5.1f}% of 74.5 TF", flush=True)
 
 
@@ -37,11 +37,11 @@ if __name__ == "__main__":
     variants = [int(x) for x in sys.argv[2].split(",")] if len(sys.argv) > 2 else [1, 2, 3, 4, 5, 6]
     for n in ns:
         for v in variants:
-            probe(n, v, 0.01, flags=4)      # general masses, softened
-            probe(n, v, 0.01)               # equal masses (Plummer): hoisted-mass kernel
+            probe(n, v, 0.01, flags=4 | 128)   # row gather, general masses, softened
+            probe(n, v, 0.01, flags=128)       # row gather, equal masses (Plummer): hoisted-mass kernel
             if len(sys.argv) > 3 and 'cut' in sys.argv[3]:
-                probe(n, v, 0.0)            # cutoff mode (reference-uniform SI bodies)
+                probe(n, v, 0.0, flags=128)  # row gather, cutoff mode (reference-uniform SI bodies)
             if len(sys.argv) > 3 and 'sym' in sys.argv[3]:
-                probe(n, v, 0.01, flags=64 | 4)   # pair-symmetric pass, general masses
-                probe(n, v, 0.01, flags=64)       # pair-symmetric pass, equal masses
-                probe(n, v, 0.0, flags=64)        # pair-symmetric pass, cutoff mode
+                probe(n, v, 0.01, flags=4)   # pair-symmetric pass, general masses
+                probe(n, v, 0.01, flags=0)       # pair-symmetric pass, equal masses
+                probe(n, v, 0.0, flags=0)        # pair-symmetric pass, cutoff mode
