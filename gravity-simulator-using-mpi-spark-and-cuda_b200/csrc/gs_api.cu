@@ -283,8 +283,10 @@ int default_variant(int n, int world, int cut_mode, uint32_t flags) {
         return units10 < 4 * 148 ? 16 : 10;
     }
     if (!(flags & GS_FLAG_DETERMINISTIC) && world <= kMaxPeers + 1) {
-        // pair-symmetric pass (R = 6 or 4, 256 threads): R = 6 unless its 1536-body tile pads this N much worse
-        const double cost6 = (double)pad6 * pad6, cost1 = (double)pad1 * pad1 / 0.95;
+        // pair-symmetric pass (256 threads; measured at N = 1M, equal masses: R = 8 4.12e12, R = 6 3.88e12,
+        // R = 4 3.66e12 interactions/s): the fastest after charging each its padded work
+        const double cost3 = (double)pad3 * pad3, cost6 = (double)pad6 * pad6 / 0.94, cost1 = (double)pad1 * pad1 / 0.89;
+        if (cost3 <= cost6 && cost3 <= cost1) return 3;
         return cost6 <= cost1 ? 6 : 1;
     }
     if (cut_mode != kSoftened) return 3;
@@ -673,7 +675,7 @@ int gs_create(gs_ctx** out, const gs_config* cfg) {
          (!c->acc_stage && !dmalloc((void**)&c->acc_stage, vel_bytes))))
         return fail(GS_ENOMEM);
     // pair-symmetric pass: wanted unless the caller asks for bit-reproducible sums; needs a 256-thread R=4/6 variant
-    c->want_sym = !(c->cfg.flags & GS_FLAG_DETERMINISTIC) && c->threads == 256 && (c->R == 4 || c->R == 6) &&
+    c->want_sym = !(c->cfg.flags & GS_FLAG_DETERMINISTIC) && c->threads == 256 && (c->R == 4 || c->R == 6 || c->R == 8) &&
                   cfg->world_size <= kMaxPeers + 1;
     if (c->want_sym) {      // allocated now so that setup_peer_exchange() can publish it to the peers
         if (!dmalloc((void**)&c->d_accj, vel_bytes)) return fail(GS_ENOMEM);

@@ -18,6 +18,7 @@
 // ranges of equal estimated cost (host-side plan, build_sym_plan); i-side sums of a row split between CTAs go
 // through the same partial-sum scratch as the row-gather kernel; sym_finish_kernel adds i-side and j-side sums
 // and finishes (integration or acceleration output).
+#include <cstdlib>
 #include <vector>
 
 #include "gs_device.cuh"
@@ -26,13 +27,16 @@ namespace gs {
 
 constexpr int kSymThreads = 256;
 constexpr int kSymWarps = kSymThreads / 32;
+constexpr int kSymDefaultNPair = 4;
 constexpr size_t kSymTileBytes = (size_t)kJTile * sizeof(float4);
 constexpr size_t kSymAccABytes = (size_t)kSymWarps * (kJTile / 2) * sizeof(float4);
 constexpr size_t kSymAccBBytes = (size_t)kSymWarps * (kJTile / 2) * sizeof(float2);
 constexpr size_t kSymSmemBytes = kStages * kSymTileBytes + 2 * kStages * sizeof(uint64_t) + 64 + kSymAccABytes + kSymAccBBytes;
 
 // One j-tile, both directions.  accA/accB: THIS warp's j-side running sums ({ax0,ax1,ay0,ay1}, {az0,az1} per j-pair).
-template <int R, int CUT, bool UNI>
+// NPAIR j-pairs per lane and iteration (pairs q, q+32, ... of a 32*NPAIR-pair chunk, q = (it + lane) mod 32):
+// more independent chains between two __syncwarp()s.
+template <int R, int CUT, bool UNI, int NPAIR>
 __device__ __forceinline__ void sym_tile(const float4* __restrict__ T, float4* __restrict__ accA,
                                          float2* __restrict__ accB, int lane, const float2 (&nxi)[R],
                                          const float2 (&nyi)[R], const float2 (&nzi)[R], const float2 (&nmui)[R],
@@ -40,17 +44,19 @@ __device__ __forceinline__ void sym_tile(const float4* __restrict__ T, float4* _
     float2 ax[R], ay[R], az[R];
 #pragma unroll
     for (int b = 0; b < R; ++b) ax[b] = ay[b] = az[b] = make_float2(0.f, 0.f);
-    for (int chunk = 0; chunk < kJTile / 128; ++chunk) {       // 64 j-pairs per chunk
+    for (int chunk = 0; chunk < kJTile / (64 * NPAIR); ++chunk) {
 #pragma unroll 1
         for (int it = 0; it < 32; ++it) {
-            const int p0 = chunk * 64 + ((it + lane) & 31);
-            const int p1 = p0 + 32;
-            float4 JA[2] = {accA[p0], accA[p1]};
-            float2 JB[2] = {accB[p0], accB[p1]};
-            const float4 A[2] = {T[2 * p0], T[2 * p1]};
-            const float4 B[2] = {T[2 * p0 + 1], T[2 * p1 + 1]};
+            const int p0 = chunk * (32 * NPAIR) + ((it + lane) & 31);
+            float4 JA[NPAIR], A[NPAIR], B[NPAIR];
+            float2 JB[NPAIR];
 #pragma unroll
-            for (int h = 0; h < 2; ++h) {
+            for (int h = 0; h < NPAIR; ++h) {
+                A[h] = T[2 * (p0 + 32 * h)]; B[h] = T[2 * (p0 + 32 * h) + 1];
+                JA[h] = accA[p0 + 32 * h]; JB[h] = accB[p0 + 32 * h];
+            }
+#pragma unroll
+            for (int h = 0; h < NPAIR; ++h) {
                 const float2 xj = make_float2(A[h].x, A[h].y), yj = make_float2(A[h].z, A[h].w);
                 const float2 zj = make_float2(B[h].x, B[h].y), mj = make_float2(B[h].z, B[h].w);
                 float2 jx = make_float2(JA[h].x, JA[h].y), jy = make_float2(JA[h].z, JA[h].w), jz = JB[h];
@@ -81,8 +87,8 @@ __device__ __forceinline__ void sym_tile(const float4* __restrict__ T, float4* _
                 JA[h] = make_float4(jx.x, jx.y, jy.x, jy.y);
                 JB[h] = jz;
             }
-            accA[p0] = JA[0]; accA[p1] = JA[1];
-            accB[p0] = JB[0]; accB[p1] = JB[1];
+#pragma unroll
+            for (int h = 0; h < NPAIR; ++h) { accA[p0 + 32 * h] = JA[h]; accB[p0 + 32 * h] = JB[h]; }
             __syncwarp();     // next iteration another lane picks these pairs up
         }
     }
@@ -94,7 +100,7 @@ __device__ __forceinline__ void sym_tile(const float4* __restrict__ T, float4* _
     }
 }
 
-template <int R, int MINB, int CUT, bool UNI>
+template <int R, int MINB, int CUT, bool UNI, int NPAIR>
 __global__ void __launch_bounds__(kSymThreads, MINB) sym_force_kernel(const SymParams p) {
     constexpr int ITILE = kSymThreads * R;
     constexpr int NP = R / 2;
@@ -170,7 +176,7 @@ __global__ void __launch_bounds__(kSymThreads, MINB) sym_force_kernel(const SymP
             const float4* T = tiles + (size_t)stage * kJTile;
             const bool symmetric = (kk >= p.diag);
             if (!symmetric) tile_packed<R, (CUT == kSoftened ? kSoftened : kCutoff), UNI, 2>(T, nxi, nyi, nzi, eps2, p.cut2, acc);
-            else sym_tile<R, CUT, UNI>(T, accA, accB, lane, nxi, nyi, nzi, nmui, eps2, p.cut2, acc);
+            else sym_tile<R, CUT, UNI, NPAIR>(T, accA, accB, lane, nxi, nyi, nzi, nmui, eps2, p.cut2, acc);
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty[stage]);
             if (symmetric) {
@@ -287,16 +293,22 @@ void build_sym_plan(const SymParams& sp, int grid, int cost_plain, int cost_sym,
 }
 
 typedef void (*SymKernel)(const SymParams);
+static int sym_npair() {       // j-pairs per lane and iteration (env GRAVSIM_SYM_NPAIR for measurements)
+    static int v = 0;
+    if (!v) { const char* e = getenv("GRAVSIM_SYM_NPAIR"); v = (e && atoi(e) == 2) ? 2 : (e && atoi(e) == 4) ? 4 : kSymDefaultNPair; }
+    return v;
+}
+template <int RR, int NP>
+static SymKernel pick_sym_rn(int cut, bool uni) {
+    if (cut == kSoftened) return uni ? (SymKernel)sym_force_kernel<RR, 1, kSoftened, true, NP>
+                                     : (SymKernel)sym_force_kernel<RR, 1, kSoftened, false, NP>;
+    return uni ? (SymKernel)sym_force_kernel<RR, 1, kCutoff, true, NP> : (SymKernel)sym_force_kernel<RR, 1, kCutoff, false, NP>;
+}
 static SymKernel pick_sym(int R, int cut, bool uni) {
-#define GS_SYM(RR, MB)                                                                                          \
-    if (R == RR) {                                                                                              \
-        if (cut == kSoftened) return uni ? (SymKernel)sym_force_kernel<RR, MB, kSoftened, true>                 \
-                                         : (SymKernel)sym_force_kernel<RR, MB, kSoftened, false>;               \
-        return uni ? (SymKernel)sym_force_kernel<RR, MB, kCutoff, true> : (SymKernel)sym_force_kernel<RR, MB, kCutoff, false>; \
-    }
-    GS_SYM(4, 1)
-    GS_SYM(6, 1)
-#undef GS_SYM
+    const int np = sym_npair();
+    if (R == 4) return np == 4 ? pick_sym_rn<4, 4>(cut, uni) : pick_sym_rn<4, 2>(cut, uni);
+    if (R == 6) return np == 4 ? pick_sym_rn<6, 4>(cut, uni) : pick_sym_rn<6, 2>(cut, uni);
+    if (R == 8) return np == 4 ? pick_sym_rn<8, 4>(cut, uni) : pick_sym_rn<8, 2>(cut, uni);
     return nullptr;
 }
 

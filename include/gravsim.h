@@ -124,7 +124,9 @@ int gs_download_aos_f64(gs_ctx *ctx, void *particles56, int n);
 /* ---- the hot path ------------------------------------------------------------------------ */
 
 /* Replaces the step loops cuda.cu:155-163 (kernel, sync, D2H, host update) and mpi.c:191-237
- * (force rows, in-place update, MPI_Allgatherv, MPI_Barrier).  All bodies advance from the
+ * (force rows, in-place update, MPI_Allgatherv, MPI_Barrier).  By default every unordered pair is
+ * evaluated once and applied to both bodies (cuda.cu:43-49, without its race; GS_FLAG_DETERMINISTIC
+ * evaluates ordered pairs like mpi.c:196-204 and is bit-reproducible).  All bodies advance from the
  * same snapshot (synchronous step; see DESIGN.md on mpi.c's in-place order).  Asynchronous:
  * returns after enqueueing; no per-step host synchronisation or D2H. */
 int gs_step(gs_ctx *ctx, int nsteps);

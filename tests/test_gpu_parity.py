@@ -193,7 +193,7 @@ def test_symmetric_pass(gs, oracle, grid, monkeypatch):
     # GS_FLAG_SYMMETRIC: every unordered pair once, both directions (floating-point atomics: tolerance, not bits)
     if grid:
         monkeypatch.setenv("GRAVSIM_GRID", str(grid))
-    for variant in (6, 1):
+    for variant in (3, 6, 1):
         b = gs.ic_reference_uniform(7001, seed=60 + variant)                 # general masses, cutoff rule, padding
         b[11] = b[5]                                                          # a coincident pair
         with gs.GravSim(7001, flags=gs.FLAG_SYMMETRIC, variant=variant) as sim:

@@ -8,8 +8,7 @@ timeout 600 python bench.py --impl reference --steps 5 --warmup 1 > gpurun_out/b
 CMD="python bench.py --steps 2 --warmup 3 --no-cpu-baseline"
 $CMD > gpurun_out/plain.log 2>&1 && ncu --metrics gpu__time_duration.sum --clock-control none -c 80 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu1.log 2>&1
 echo "ncu1 rc=$?"
-$CMD > gpurun_out/plain2.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:force_step -s 3 -c 1 -o gpurun_out/prof $CMD > gpurun_out/ncu2.log 2>&1
+$CMD > gpurun_out/plain2.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:sym_force -s 3 -c 1 -o gpurun_out/prof $CMD > gpurun_out/ncu2.log 2>&1
 echo "ncu2 rc=$?"
-./tools/microbench/fp32_pipes > gpurun_out/microbench.txt 2>&1
 timeout 600 python tests/reference_configs.py > gpurun_out/reference_configs.json 2> gpurun_out/refcfg.err
-timeout 300 python tools/perf_probe.py 1048576 6,3,7,1 cut > gpurun_out/probe_1m.txt 2>&1; cat gpurun_out/probe_1m.txt
+timeout 300 python tools/perf_probe.py 1048576 0 sym > gpurun_out/probe_1m.txt 2>&1; cat gpurun_out/probe_1m.txt
