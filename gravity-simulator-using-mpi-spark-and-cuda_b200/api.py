@@ -35,6 +35,7 @@ EXPORTED_SYMBOLS = [
     "gs_get_info", "gs_kernel_launches", "gs_last_cuda_error", "gs_strerror", "gs_version",
     "gs_host_alloc", "gs_host_free",
     "gs_plan_slice", "gs_plan_cta_range", "gs_plan_tile_owners", "gs_plan_tiles",
+    "gs_plan_sym_row", "gs_plan_sym_unit", "gs_plan_sym_cta",
     "gs_ic_reference_uniform_f32", "gs_ic_reference_uniform_f64", "gs_ic_plummer_f32",
     "gs_ic_two_galaxy_f32",
     "gs_state_write", "gs_state_read_header", "gs_state_read",
@@ -133,6 +134,9 @@ def lib():
     L.gs_plan_cta_range.argtypes = [C.c_int64, C.c_int64, C.c_int, C.c_int, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
     L.gs_plan_tile_owners.argtypes = [C.c_int64, C.c_int64, C.c_int, C.c_int64] + [C.POINTER(C.c_int)] * 3
     L.gs_plan_tiles.argtypes = [C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    L.gs_plan_sym_row.argtypes = [C.c_int] * 5 + [C.POINTER(C.c_int)] * 3
+    L.gs_plan_sym_unit.argtypes = [C.c_int] * 6 + [C.POINTER(C.c_int)]
+    L.gs_plan_sym_cta.argtypes = [C.c_int] * 6 + [C.POINTER(C.c_int)] * 3
     L.gs_ic_reference_uniform_f32.argtypes = [C.c_void_p, C.c_int, C.c_uint64]
     L.gs_ic_reference_uniform_f64.argtypes = [C.c_void_p, C.c_int, C.c_uint64]
     L.gs_ic_plummer_f32.argtypes = [C.c_void_p, C.c_int, C.c_uint64, C.c_double]
@@ -203,6 +207,24 @@ def plan_tile_owners(ni_tiles, nj_tiles, grid, it):
     _check(lib().gs_plan_tile_owners(ni_tiles, nj_tiles, grid, it, C.byref(a), C.byref(b), C.byref(s)),
            "gs_plan_tile_owners")
     return a.value, b.value, bool(s.value)
+
+
+def plan_sym_row(n, world_size, rank, variant, row):
+    a, b, c = C.c_int(), C.c_int(), C.c_int()
+    _check(lib().gs_plan_sym_row(n, world_size, rank, variant, row, C.byref(a), C.byref(b), C.byref(c)), "gs_plan_sym_row")
+    return a.value, b.value, c.value          # rows of the rank, units of this row, leading plain units
+
+
+def plan_sym_unit(n, world_size, rank, variant, row, k):
+    j = C.c_int()
+    _check(lib().gs_plan_sym_unit(n, world_size, rank, variant, row, k, C.byref(j)), "gs_plan_sym_unit")
+    return j.value
+
+
+def plan_sym_cta(n, world_size, rank, variant, grid, cta):
+    a, b, c = C.c_int(), C.c_int(), C.c_int()
+    _check(lib().gs_plan_sym_cta(n, world_size, rank, variant, grid, cta, C.byref(a), C.byref(b), C.byref(c)), "gs_plan_sym_cta")
+    return a.value, b.value, c.value
 
 
 def nccl_unique_id():

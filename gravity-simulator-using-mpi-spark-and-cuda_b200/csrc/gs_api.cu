@@ -521,6 +521,54 @@ int gs_plan_tile_owners(int64_t ni_tiles, int64_t nj_tiles, int grid, int64_t it
     return GS_OK;
 }
 
+// ---- pair-symmetric plan, host side (CPU-testable) ----------------------------------------------------
+static int sym_geometry_for(int n, int world, int rank, int variant, SymParams* sp) {
+    VariantInfo vi;
+    if (variant == 0) variant = 3;
+    if (!variant_info(variant, &vi) || world < 1 || rank < 0 || rank >= world) return GS_EINVAL;
+    int n_pad = 0, b = 0, e = 0;
+    if (gs_plan_slice(n, world, rank, variant, &n_pad, &b, &e) != GS_OK) return GS_EINVAL;
+    gs_ctx tmp;
+    tmp.cfg.world_size = world; tmp.cfg.rank = rank;
+    tmp.n = n; tmp.i_begin = b; tmp.slice = e - b; tmp.i_tile = vi.i_tile;
+    fill_sym_geometry(&tmp, sp);
+    return GS_OK;
+}
+
+int gs_plan_sym_row(int n, int world_size, int rank, int variant, int row, int* n_rows, int* n_units, int* n_plain) {
+    SymParams sp;
+    int rc = sym_geometry_for(n, world_size, rank, variant, &sp);
+    if (rc != GS_OK) return rc;
+    if (row < 0 || row >= sp.ni_tiles) return GS_EINVAL;
+    if (n_rows) *n_rows = sp.ni_tiles;
+    if (n_units) *n_units = sym_row_units(sp, row);
+    if (n_plain) *n_plain = sp.diag;
+    return GS_OK;
+}
+
+int gs_plan_sym_unit(int n, int world_size, int rank, int variant, int row, int k, int* j_tile) {
+    SymParams sp;
+    int rc = sym_geometry_for(n, world_size, rank, variant, &sp);
+    if (rc != GS_OK) return rc;
+    if (row < 0 || row >= sp.ni_tiles || k < 0 || k >= sym_row_units(sp, row) || !j_tile) return GS_EINVAL;
+    *j_tile = sym_unit_tile(sp, row, k);
+    return GS_OK;
+}
+
+int gs_plan_sym_cta(int n, int world_size, int rank, int variant, int grid, int cta, int* row0, int* k0, int* count) {
+    SymParams sp;
+    int rc = sym_geometry_for(n, world_size, rank, variant, &sp);
+    if (rc != GS_OK) return rc;
+    if (grid < 1 || cta < 0 || cta >= grid) return GS_EINVAL;
+    std::vector<SymCta> hc;
+    std::vector<int2> hr;
+    build_sym_plan(sp, grid, 100, 133, hc, hr);
+    if (row0) *row0 = hc[cta].row0;
+    if (k0) *k0 = hc[cta].k0;
+    if (count) *count = hc[cta].count;
+    return GS_OK;
+}
+
 int gs_nccl_unique_id(void* out_id) {
     if (!out_id) return GS_EINVAL;
     NcclApi& nc = nccl_api();

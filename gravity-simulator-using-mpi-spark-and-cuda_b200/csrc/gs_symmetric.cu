@@ -1,5 +1,5 @@
-// gs_symmetric.cu -- pair-symmetric force pass (GS_FLAG_SYMMETRIC, one GPU): every unordered pair of
-// bodies in different tiles is evaluated ONCE and applied to both bodies (Newton's third law), which the
+// gs_symmetric.cu -- pair-symmetric force pass (the default; GS_FLAG_DETERMINISTIC turns it off): every unordered
+// pair of bodies in different tiles is evaluated ONCE and applied to both bodies (Newton's third law), which the
 // reference's cuda.cu also does (cuda.cu:43-49) -- there with a data race, here without.
 //
 // Why it pays: the kernel is issue-bound.  A (i-body, j-pair) step costs 26 issue cycles for
@@ -10,11 +10,13 @@
 // warp touch the same j at the same time and each lane simply read-modify-writes that pair's running sums in a
 // per-warp shared-memory accumulator array (conflict-free: consecutive lanes, consecutive entries).
 // After a j-tile the eight warps' arrays are added up and sent to global memory with atomic adds
-// (floating-point atomics: the pass is NOT bit-reproducible, which is why it is opt-in).
+// (floating-point atomics: the last bits depend on timing; local memory, or NVLink peer memory when the j-bodies
+// belong to another GPU).
 //
 // Work: rows of (i-tile x j-tile) units; row I starts with its `diag` = i_tile/j_tile own j-tiles, done as
-// plain (one-directional, all ordered pairs) units, followed by symmetric units for every j-tile after them;
-// j-tiles before them are covered by earlier rows.  Units are handed to the persistent CTAs as contiguous
+// plain (one-directional, all ordered pairs) units, followed by symmetric units for every later j-tile of the
+// rank's slice (earlier ones are covered by earlier rows) and, on P GPUs, for the next floor((P-1)/2) slices and
+// half of the opposite one (SymParams, sym_row_units/sym_unit_tile in gs_kernels.h).  Units are handed to the persistent CTAs as contiguous
 // ranges of equal estimated cost (host-side plan, build_sym_plan); i-side sums of a row split between CTAs go
 // through the same partial-sum scratch as the row-gather kernel; sym_finish_kernel adds i-side and j-side sums
 // and finishes (integration or acceleration output).

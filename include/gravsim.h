@@ -193,6 +193,12 @@ int gs_plan_cta_range(int64_t ni_tiles, int64_t nj_tiles, int grid, int cta, int
 int gs_plan_tile_owners(int64_t ni_tiles, int64_t nj_tiles, int grid, int64_t it,
                         int *cta_first, int *cta_last, int *is_split);
 int gs_plan_tiles(int variant, int *i_tile, int *j_tile);
+/* Pair-symmetric pass: rows of `rank` (one per i-tile), units of a row (the first n_plain are
+ * one-directional units on the row's own j-tiles), the global j-tile of a unit, and the unit range of a
+ * persistent CTA.  Every unordered pair of bodies is covered exactly once over all ranks. */
+int gs_plan_sym_row(int n, int world_size, int rank, int variant, int row, int *n_rows, int *n_units, int *n_plain);
+int gs_plan_sym_unit(int n, int world_size, int rank, int variant, int row, int k, int *j_tile);
+int gs_plan_sym_cta(int n, int world_size, int rank, int variant, int grid, int cta, int *row0, int *k0, int *count);
 
 /* ---- host utilities: initial conditions, state files, reference-format dumps -------------- */
 /* (plain C, no GPU needed) */

@@ -68,6 +68,54 @@ def test_stream_k_partition_covers_every_unit_once(gs, ni, nj, grid):
             assert min(tiles) == ranges[c][0] // nj
 
 
+@pytest.mark.parametrize("world", [1, 2, 3, 4, 5, 8])
+@pytest.mark.parametrize("variant", [3, 6])
+def test_symmetric_plan_covers_every_pair_once(gs, world, variant):
+    # pair-symmetric pass: over all ranks every unordered pair of bodies must be evaluated exactly once.
+    # At tile level: count[(i-tile row as j-tile range, j-tile)] -- plain units cover a row's own j-tiles in
+    # one direction (both orders inside the row's bodies), symmetric units cover (row, other j-tile) once.
+    i_tile, j_tile = gs.plan_tiles(variant)
+    diag = i_tile // j_tile
+    n = 4 * i_tile * world - 5                       # 4 rows per rank, a little padding
+    n_pad = gs.plan_slice(n, world, 0, variant)[0]
+    njt = n_pad // j_tile
+    seen = np.zeros((njt, njt), dtype=np.int32)      # [j-tile a][j-tile b], a != b: symmetric coverage
+    for rank in range(world):
+        rows = gs.plan_sym_row(n, world, rank, variant, 0)[0]
+        assert rows == n_pad // world // i_tile
+        for row in range(rows):
+            _, units, plain = gs.plan_sym_row(n, world, rank, variant, row)
+            assert plain == diag
+            own = [(rank * rows + row) * diag + d for d in range(diag)]      # the row's own j-tiles
+            for k in range(units):
+                jt = gs.plan_sym_unit(n, world, rank, variant, row, k)
+                if k < plain:
+                    assert jt == own[k]                                         # one-directional, all ordered pairs
+                else:
+                    assert jt not in own
+                    for a in own:
+                        seen[min(a, jt), max(a, jt)] += 1
+    iu = np.triu_indices(njt, 1)
+    same_row = (iu[0] // diag) == (iu[1] // diag)       # pairs of j-tiles inside one row are done by its plain units
+    assert (seen[iu][~same_row] == 1).all() and (seen[iu][same_row] == 0).all()
+    # and the CTA ranges of one rank tile its units exactly once
+    grid = 37
+    total = sum(gs.plan_sym_row(n, world, 0, variant, r)[1] for r in range(rows))
+    pos, count = (0, 0), 0
+    for cta in range(grid):
+        row0, k0, cnt = gs.plan_sym_cta(n, world, 0, variant, grid, cta)
+        if cnt:
+            assert (row0, k0) == pos
+            for _ in range(cnt):
+                r, k = pos
+                k += 1
+                if k >= gs.plan_sym_row(n, world, 0, variant, r)[1]:
+                    r, k = r + 1, 0
+                pos = (r, k)
+        count += cnt
+    assert count == total
+
+
 def test_slices_tile_aligned_and_cover(gs):
     for variant in (1, 3, 5, 6, 7, 10, 11, 12, 13, 16):
         it, jt = gs.plan_tiles(variant)
