@@ -17,13 +17,11 @@ _REPO = os.path.dirname(_HERE)
 INTEGRATOR_EULER = 0
 INTEGRATOR_LEAPFROG = 1
 G_SI = 6.67430e-11          # cuda.cu:11, mpi.c:9
-FLAG_NO_OVERLAP = 1
 FLAG_TWO_PASS = 2
 FLAG_NO_UNIFORM_MASS = 4
 FLAG_OVERLAP = 8
 FLAG_NCCL_EXCHANGE = 16
 FLAG_COMPENSATED = 32
-FLAG_SYMMETRIC = 64
 FLAG_DETERMINISTIC = 128
 NCCL_ID_BYTES = 128
 

@@ -72,9 +72,9 @@ struct gs_ctx {
     float4* h_snap[2] = {nullptr, nullptr};
     cudaEvent_t ev_snap_ready[2] = {nullptr, nullptr}, ev_snap_done[2] = {nullptr, nullptr};
     bool buf_copy_pending[2] = {false, false};   // pos[b] is still being read by a snapshot copy
-    // pair-symmetric pass (GS_FLAG_SYMMETRIC, one GPU)
+    // pair-symmetric pass (the default)
     bool symmetric = false;
-    int sym_grid = 0, sym_regs = 0;
+    int sym_grid = 0, sym_regs = 0, sym_cut_mode = 0;
     SymCta* d_sym_ctas = nullptr;
     int2* d_sym_rows = nullptr;
     float* d_accj = nullptr;                    // j-side sums of MY bodies (peers add into it over NVLink)
@@ -173,7 +173,7 @@ int force_pass(gs_ctx* c, int final_mode, float kick, float drift, float4* acc_o
     }
     // two passes (own j-slice first, the rest once the peers' bodies are in): GS_FLAG_OVERLAP on several
     // GPUs, or GS_FLAG_TWO_PASS (same code path on one GPU, for tests)
-    const bool two_pass = ((W > 1) && (c->cfg.flags & GS_FLAG_OVERLAP) && !(c->cfg.flags & GS_FLAG_NO_OVERLAP)) ||
+    const bool two_pass = ((W > 1) && (c->cfg.flags & GS_FLAG_OVERLAP)) ||
                           ((W == 1) && (c->cfg.flags & GS_FLAG_TWO_PASS) && p.nj_total >= 2);
     int rc;
     // On several GPUs with the peer-memory exchange the integrating pass is finished by the finish kernel
@@ -204,7 +204,7 @@ int force_pass(gs_ctx* c, int final_mode, float kick, float drift, float4* acc_o
             sp.pos = c->pos[c->cur]; sp.acc_whole = c->acc_stage; sp.partial = c->sym_partial;
             for (int q = 0; q < W; ++q) sp.accj[q] = c->peer_accj[q];
             sp.ctas = c->d_sym_ctas; sp.eps2 = c->eps2; sp.cut2 = c->cut2; sp.mu_uniform = c->mu_uniform;
-            GS_CUDA(c, launch_sym_force(c->R, c->cut_mode, sp, c->sym_grid, c->stream)); c->launches++;
+            GS_CUDA(c, launch_sym_force(c->R, c->threads, c->sym_cut_mode, sp, c->sym_grid, c->stream)); c->launches++;
             if (W > 1) {    // my j-side sums are complete once every peer's force kernel has finished
                 PeerFlags f;
                 for (int q = 0; q < W; ++q) f.slot[q] = c->peer_flags[q] + 16 + c->cfg.rank;
@@ -411,9 +411,12 @@ void peer_exchange_goodbye(gs_ctx* c) {
 int setup_symmetric(gs_ctx* c) {
     if (!c->want_sym) return GS_OK;
     if (c->cfg.world_size > 1 && !(c->p2p && c->p2p_atomics)) return GS_OK;     // stay on the row-gather kernel
-    if (c->cut_mode == kCutoffTracked) c->cut_mode = kCutoff;
+    // eps == 0: select-free pass + exact redo of the rare units where two bodies coincide; in a symmetric unit no
+    // body meets itself, so (unlike the row-gather kernel's diagonal tiles) there is no systematic extra work
+    const char* ecm = getenv("GRAVSIM_CUTMODE");
+    c->sym_cut_mode = (c->cfg.eps > 0.0) ? kSoftened : (ecm && !strcmp(ecm, "select")) ? kCutoff : kCutoffTracked;
     int ctas = 0;
-    cudaError_t e = sym_kernel_setup(c->R, c->cut_mode, &ctas, &c->sym_regs);
+    cudaError_t e = sym_kernel_setup(c->R, c->threads, c->sym_cut_mode, &ctas, &c->sym_regs);
     if (e != cudaSuccess || ctas < 1) { c->last_cuda_error = (int)e; return GS_ECUDA; }
     c->sym_grid = c->sm_count * ctas;
     const char* eg = getenv("GRAVSIM_GRID");
@@ -723,7 +726,7 @@ int gs_create(gs_ctx** out, const gs_config* cfg) {
          (!c->acc_stage && !dmalloc((void**)&c->acc_stage, vel_bytes))))
         return fail(GS_ENOMEM);
     // pair-symmetric pass: wanted unless the caller asks for bit-reproducible sums; needs a 256-thread R=4/6 variant
-    c->want_sym = !(c->cfg.flags & GS_FLAG_DETERMINISTIC) && c->threads == 256 && (c->R == 4 || c->R == 6 || c->R == 8) &&
+    c->want_sym = !(c->cfg.flags & GS_FLAG_DETERMINISTIC) && sym_supported(c->R, c->threads) &&
                   cfg->world_size <= kMaxPeers + 1;
     if (c->want_sym) {      // allocated now so that setup_peer_exchange() can publish it to the peers
         if (!dmalloc((void**)&c->d_accj, vel_bytes)) return fail(GS_ENOMEM);

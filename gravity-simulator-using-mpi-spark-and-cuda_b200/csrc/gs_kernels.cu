@@ -183,7 +183,8 @@ __global__ void __launch_bounds__(256) fixup_kernel(const StepParams p, int grid
     X(13, 2, 512, 2, 1, 2) \
     X(14, 6, 256, 1, 1, 1) \
     X(15, 8, 128, 2, 1, 1) \
-    X(16, 2, 128, 5, 1, 2)
+    X(16, 2, 128, 5, 1, 2) \
+    X(17, 8, 384, 1, 1, 1)
 
 bool variant_info(int variant, VariantInfo* out) {
     switch (variant) {

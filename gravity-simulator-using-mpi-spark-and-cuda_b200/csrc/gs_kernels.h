@@ -15,7 +15,7 @@ enum CutMode : int { kSoftened = 0,        // eps > 0
 
 // Kernel variants (gs_config.variant / env GRAVSIM_VARIANT): i-bodies per thread R, CTA size, inner
 // unroll, packed f32x2 or scalar arithmetic.  The table lives in gs_kernels.cu (GS_VARIANTS).
-constexpr int kNumVariants = 16;
+constexpr int kNumVariants = 17;
 constexpr int kDefaultVariant = 1;
 constexpr float kPadPosition = 1.0e18f;   // padding bodies: (1e18,1e18,1e18), mu = 0
 struct VariantInfo { int R, threads, unroll, packed, i_tile; };
@@ -71,7 +71,7 @@ cudaError_t launch_signal_peers(const PeerFlags& f, int world, int my_rank, uint
 cudaError_t launch_wait_flags(const uint32_t* my_flags, int world, int my_rank, uint32_t value,
                               unsigned long long timeout_ns, uint32_t* err, cudaStream_t s);
 
-// ---- pair-symmetric force pass (gs_symmetric.cu; GS_FLAG_SYMMETRIC, one GPU) --------------------------------
+// ---- pair-symmetric force pass (gs_symmetric.cu; the default) --------------------------------------------------
 struct SymCta { int row0, k0, count, pad; };   // a persistent CTA's first unit (row, index in the row) and unit count
 struct SymParams {
     const float4* pos;       // packed pairs, n_pad bodies (every rank's)
@@ -111,14 +111,16 @@ GS_HD int sym_unit_tile(const SymParams& p, int row, int k) {
     const int opposite = (p.rank + p.world / 2) % p.world;
     return opposite * p.slice_tiles + (p.half_mode == 2 ? p.half_rows * p.diag : 0) + k;
 }
-size_t sym_smem_bytes();
-cudaError_t sym_kernel_setup(int R, int cut_mode, int* ctas_per_sm, int* regs);
-cudaError_t launch_sym_force(int R, int cut_mode, const SymParams& p, int grid, cudaStream_t s);
+bool sym_supported(int R, int threads);     // is the pass built for this (i-bodies per thread, CTA size)?
+size_t sym_smem_bytes(int threads);
+// cut_mode: CutMode (kCutoffTracked = select-free pass + exact redo of the units where two bodies coincide)
+cudaError_t sym_kernel_setup(int R, int threads, int cut_mode, int* ctas_per_sm, int* regs);
+cudaError_t launch_sym_force(int R, int threads, int cut_mode, const SymParams& p, int grid, cudaStream_t s);
 cudaError_t launch_sym_finish(const StepParams& p, const SymParams& sp, const int2* rows, int i_tile,
                               const FinishExtras* extras, cudaStream_t s);
 
 // AoS <-> packed-pair conversion on the device. `aos` is the raw byte image of the reference's
-// 28-byte (f32) or 56-byte (f64) records.  Bodies >= n are padding (mu = 0, at the origin).
+// 28-byte (f32) or 56-byte (f64) records.  Bodies >= n are padding (mu = 0, at kPadPosition).
 // pos_lo_local / vel_lo_local (nullable): low-order words, i.e. what rounding the record to fp32 dropped.
 cudaError_t launch_aos_to_packed(const void* aos, int record_bytes, int n, int n_pad, double G,
                                  float4* pos, float4* vel_local, double* mass, int i_begin,

@@ -27,25 +27,45 @@
 
 namespace gs {
 
-constexpr int kSymThreads = 256;
-constexpr int kSymWarps = kSymThreads / 32;
 constexpr int kSymDefaultNPair = 4;
 constexpr size_t kSymTileBytes = (size_t)kJTile * sizeof(float4);
-constexpr size_t kSymAccABytes = (size_t)kSymWarps * (kJTile / 2) * sizeof(float4);
-constexpr size_t kSymAccBBytes = (size_t)kSymWarps * (kJTile / 2) * sizeof(float2);
-constexpr size_t kSymSmemBytes = kStages * kSymTileBytes + 2 * kStages * sizeof(uint64_t) + 64 + kSymAccABytes + kSymAccBBytes;
+constexpr size_t kSymAccBytesPerWarp = (size_t)(kJTile / 2) * (sizeof(float4) + sizeof(float2));
+constexpr size_t sym_smem_for(int threads) {
+    return kStages * kSymTileBytes + 2 * kStages * sizeof(uint64_t) + 64 + (size_t)(threads / 32) * kSymAccBytesPerWarp;
+}
+
+// How the reference's "r < 1e-10 contributes nothing" (cuda.cu:39, mpi.c:64) is applied inside a symmetric unit
+// when eps == 0:
+//   kSymSelect: rinv = (r^2 >= 1e-20) ? rsqrt(r^2) : 0 on every interaction (2 FSETP + 2 FSEL per j-pair and i-body);
+//   kSymTrack : no select; one FMNMX3 per j-pair and i-body remembers the smallest r^2 the lane saw, and the warp
+//               redoes the unit with kSymSelect when anything came closer than the cutoff.  In a symmetric unit the
+//               i-tile and the j-tile are different tiles, so a body never meets itself there: a redo needs two
+//               distinct bodies within 1e-10 of each other, i.e. (in fp32) coincident bodies.
+enum SymCut : int { kSymSoft = 0, kSymSelect = 1, kSymTrack = 2 };
 
 // One j-tile, both directions.  accA/accB: THIS warp's j-side running sums ({ax0,ax1,ay0,ay1}, {az0,az1} per j-pair).
 // NPAIR j-pairs per lane and iteration (pairs q, q+32, ... of a 32*NPAIR-pair chunk, q = (it + lane) mod 32):
 // more independent chains between two __syncwarp()s.
-template <int R, int CUT, bool UNI, int NPAIR>
-__device__ __forceinline__ void sym_tile(const float4* __restrict__ T, float4* __restrict__ accA,
+// Returns true (warp-uniform, kSymTrack only) when the unit has to be redone with the select; `out` is then untouched
+// and the warp's accA/accB hold garbage.
+template <int R, int CUT, bool UNI, int NPAIR, int PROBE = 0>
+__device__ __forceinline__ bool sym_tile(const float4* __restrict__ T, float4* __restrict__ accA,
                                          float2* __restrict__ accB, int lane, const float2 (&nxi)[R],
                                          const float2 (&nyi)[R], const float2 (&nzi)[R], const float2 (&nmui)[R],
                                          float2 eps2, float cut2, Acc<R>& out) {
     float2 ax[R], ay[R], az[R];
+    float rmin[NPAIR];
 #pragma unroll
     for (int b = 0; b < R; ++b) ax[b] = ay[b] = az[b] = make_float2(0.f, 0.f);
+#pragma unroll
+    for (int h = 0; h < NPAIR; ++h) rmin[h] = 3.0e38f;
+    // PROBE (timing experiments only, results are wrong): 1 = j-side sums never leave the registers (no LDS/STS
+    // round trip, no __syncwarp), 2 = j-tile read as if A and B records were de-interleaved (conflict-free), 3 = both
+    float4 PJA[NPAIR]; float2 PJB[NPAIR];
+    if (PROBE & 1) {
+#pragma unroll
+        for (int h = 0; h < NPAIR; ++h) { PJA[h] = make_float4(0.f, 0.f, 0.f, 0.f); PJB[h] = make_float2(0.f, 0.f); }
+    }
     for (int chunk = 0; chunk < kJTile / (64 * NPAIR); ++chunk) {
 #pragma unroll 1
         for (int it = 0; it < 32; ++it) {
@@ -54,8 +74,10 @@ __device__ __forceinline__ void sym_tile(const float4* __restrict__ T, float4* _
             float2 JB[NPAIR];
 #pragma unroll
             for (int h = 0; h < NPAIR; ++h) {
-                A[h] = T[2 * (p0 + 32 * h)]; B[h] = T[2 * (p0 + 32 * h) + 1];
-                JA[h] = accA[p0 + 32 * h]; JB[h] = accB[p0 + 32 * h];
+                if (PROBE & 2) { A[h] = T[p0 + 32 * h]; B[h] = T[kJTile / 2 + p0 + 32 * h]; }
+                else { A[h] = T[2 * (p0 + 32 * h)]; B[h] = T[2 * (p0 + 32 * h) + 1]; }
+                if (PROBE & 1) { JA[h] = PJA[h]; JB[h] = PJB[h]; }
+                else { JA[h] = accA[p0 + 32 * h]; JB[h] = accB[p0 + 32 * h]; }
             }
 #pragma unroll
             for (int h = 0; h < NPAIR; ++h) {
@@ -71,10 +93,11 @@ __device__ __forceinline__ void sym_tile(const float4* __restrict__ T, float4* _
                     r2 = __ffma2_rn(dy, dy, r2);
                     r2 = __ffma2_rn(dz, dz, r2);
                     float2 ri = make_float2(rsqrt_approx(r2.x), rsqrt_approx(r2.y));
-                    if (CUT != kSoftened) {
+                    if (CUT == kSymSelect) {
                         ri.x = (r2.x >= cut2) ? ri.x : 0.f;
                         ri.y = (r2.y >= cut2) ? ri.y : 0.f;
                     }
+                    if (CUT == kSymTrack) asm("min.f32 %0, %0, %1, %2;" : "+f"(rmin[h]) : "f"(r2.x), "f"(r2.y));   // FMNMX3
                     const float2 ri2 = __fmul2_rn(ri, ri);
                     const float2 t = __fmul2_rn(ri2, ri);                       // rinv^3, shared by both directions
                     const float2 s = UNI ? t : __fmul2_rn(mj, t);               // on i:  +mu_j t d
@@ -90,9 +113,22 @@ __device__ __forceinline__ void sym_tile(const float4* __restrict__ T, float4* _
                 JB[h] = jz;
             }
 #pragma unroll
-            for (int h = 0; h < NPAIR; ++h) { accA[p0 + 32 * h] = JA[h]; accB[p0 + 32 * h] = JB[h]; }
-            __syncwarp();     // next iteration another lane picks these pairs up
+            for (int h = 0; h < NPAIR; ++h) {
+                if (PROBE & 1) { PJA[h] = JA[h]; PJB[h] = JB[h]; }
+                else { accA[p0 + 32 * h] = JA[h]; accB[p0 + 32 * h] = JB[h]; }
+            }
+            if (!(PROBE & 1)) __syncwarp();     // next iteration another lane picks these pairs up
         }
+    }
+    if (PROBE & 1) {
+#pragma unroll
+        for (int h = 0; h < NPAIR; ++h) { accA[lane + 32 * h] = PJA[h]; accB[lane + 32 * h] = PJB[h]; }
+    }
+    if (CUT == kSymTrack) {
+        float m = rmin[0];
+#pragma unroll
+        for (int h = 1; h < NPAIR; ++h) m = fminf(m, rmin[h]);
+        if (__any_sync(0xffffffffu, !(m >= cut2))) return true;
     }
 #pragma unroll
     for (int b = 0; b < R; ++b) {
@@ -100,18 +136,20 @@ __device__ __forceinline__ void sym_tile(const float4* __restrict__ T, float4* _
         out.y[b] += ay[b].x + ay[b].y;
         out.z[b] += az[b].x + az[b].y;
     }
+    return false;
 }
 
-template <int R, int MINB, int CUT, bool UNI, int NPAIR>
-__global__ void __launch_bounds__(kSymThreads, MINB) sym_force_kernel(const SymParams p) {
-    constexpr int ITILE = kSymThreads * R;
+template <int R, int THREADS, int CUT, bool UNI, int NPAIR, int PROBE = 0>
+__global__ void __launch_bounds__(THREADS, 1) sym_force_kernel(const SymParams p) {
+    constexpr int ITILE = THREADS * R;
     constexpr int NP = R / 2;
+    constexpr int WARPS = THREADS / 32;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     float4* tiles = reinterpret_cast<float4*>(smem_raw);
     uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + kStages * kSymTileBytes);
     uint64_t* empty = full + kStages;
     float4* accA_all = reinterpret_cast<float4*>(smem_raw + kStages * kSymTileBytes + 2 * kStages * sizeof(uint64_t) + 64);
-    float2* accB_all = reinterpret_cast<float2*>(reinterpret_cast<unsigned char*>(accA_all) + kSymAccABytes);
+    float2* accB_all = reinterpret_cast<float2*>(accA_all + (size_t)WARPS * (kJTile / 2));
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const SymCta me = p.ctas[blockIdx.x];
@@ -124,7 +162,7 @@ __global__ void __launch_bounds__(kSymThreads, MINB) sym_force_kernel(const SymP
 #pragma unroll
         for (int s = 0; s < kStages; ++s) {
             mbar_init(&full[s], 1);
-            mbar_init(&empty[s], kSymWarps);
+            mbar_init(&empty[s], WARPS);
         }
         fence_mbar_init();
     }
@@ -157,7 +195,7 @@ __global__ void __launch_bounds__(kSymThreads, MINB) sym_force_kernel(const SymP
         Acc<R> acc;
 #pragma unroll
         for (int q = 0; q < NP; ++q) {
-            const int pair = (p.i_begin >> 1) + row * (ITILE / 2) + q * kSymThreads + tid;
+            const int pair = (p.i_begin >> 1) + row * (ITILE / 2) + q * THREADS + tid;
             const float4 A = p.pos[2 * pair], B = p.pos[2 * pair + 1];
             nxi[2 * q] = make_float2(-A.x, -A.x); nxi[2 * q + 1] = make_float2(-A.y, -A.y);
             nyi[2 * q] = make_float2(-A.z, -A.z); nyi[2 * q + 1] = make_float2(-A.w, -A.w);
@@ -177,31 +215,44 @@ __global__ void __launch_bounds__(kSymThreads, MINB) sym_force_kernel(const SymP
             mbar_wait(&full[stage], (uint32_t)((k / kStages) & 1));
             const float4* T = tiles + (size_t)stage * kJTile;
             const bool symmetric = (kk >= p.diag);
-            if (!symmetric) tile_packed<R, (CUT == kSoftened ? kSoftened : kCutoff), UNI, 2>(T, nxi, nyi, nzi, eps2, p.cut2, acc);
-            else sym_tile<R, CUT, UNI, NPAIR>(T, accA, accB, lane, nxi, nyi, nzi, nmui, eps2, p.cut2, acc);
+            if (!symmetric) {
+                // the row's own j-tiles hold the i-bodies themselves: one direction, select on every interaction
+                tile_packed<R, (CUT == kSymSoft ? kSoftened : kCutoff), UNI, 2>(T, nxi, nyi, nzi, eps2, p.cut2, acc);
+            } else if (sym_tile<R, CUT, UNI, NPAIR, PROBE>(T, accA, accB, lane, nxi, nyi, nzi, nmui, eps2, p.cut2, acc)) {
+                // kSymTrack only: something of this warp came within the cutoff (coincident bodies) -- exact redo
+                for (int e = lane; e < kJTile / 2; e += 32) {
+                    accA[e] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    accB[e] = make_float2(0.f, 0.f);
+                }
+                __syncwarp();
+                sym_tile<R, kSymSelect, UNI, (CUT == kSymTrack ? 2 : NPAIR)>(T, accA, accB, lane, nxi, nyi, nzi, nmui, eps2,
+                                                                           p.cut2, acc);
+            }
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty[stage]);
             if (symmetric) {
-                // j-side sums of this tile: add the eight warps' arrays, send them off, clear them
+                // j-side sums of this tile: add the warps' arrays, send them off, clear them
                 __syncthreads();
                 const int jtile = sym_unit_tile(p, row, kk);
                 const int owner = jtile / p.slice_tiles;                   // whose bodies these are: local or NVLink peer memory
                 float* const jbase = p.accj[owner] + 4 * (size_t)(jtile - owner * p.slice_tiles) * kJTile;
                 const float w = UNI ? -p.mu_uniform : 1.f;
-                for (int e = tid; e < kJTile / 2; e += kSymThreads) {
+                for (int e = tid; e < kJTile / 2; e += THREADS) {
                     float4 SA = make_float4(0.f, 0.f, 0.f, 0.f);
                     float2 SB = make_float2(0.f, 0.f);
 #pragma unroll
-                    for (int wv = 0; wv < kSymWarps; ++wv) {
+                    for (int wv = 0; wv < WARPS; ++wv) {
                         const float4 a = accA_all[wv * (kJTile / 2) + e];
                         const float2 b = accB_all[wv * (kJTile / 2) + e];
                         SA.x += a.x; SA.y += a.y; SA.z += a.z; SA.w += a.w; SB.x += b.x; SB.y += b.y;
                         accA_all[wv * (kJTile / 2) + e] = make_float4(0.f, 0.f, 0.f, 0.f);
                         accB_all[wv * (kJTile / 2) + e] = make_float2(0.f, 0.f);
                     }
+                    // System scope: the owner's SMs and every peer's add into the same words, over NVLink for a
+                    // remote owner; only system-scope atomics are guaranteed atomic across GPUs (SASS: RED...SYS).
                     float* dst = jbase + 4 * (2 * e);                          // bodies 2e, 2e+1 of the tile
-                    atomicAdd(dst + 0, w * SA.x); atomicAdd(dst + 1, w * SA.z); atomicAdd(dst + 2, w * SB.x);
-                    atomicAdd(dst + 4, w * SA.y); atomicAdd(dst + 5, w * SA.w); atomicAdd(dst + 6, w * SB.y);
+                    atomicAdd_system(dst + 0, w * SA.x); atomicAdd_system(dst + 1, w * SA.z); atomicAdd_system(dst + 2, w * SB.x);
+                    atomicAdd_system(dst + 4, w * SA.y); atomicAdd_system(dst + 5, w * SA.w); atomicAdd_system(dst + 6, w * SB.y);
                 }
                 __syncthreads();
             }
@@ -210,7 +261,7 @@ __global__ void __launch_bounds__(kSymThreads, MINB) sym_force_kernel(const SymP
         // i-side sums of this row segment
 #pragma unroll
         for (int q = 0; q < NP; ++q) {
-            const int in_tile = 2 * (q * kSymThreads + tid);
+            const int in_tile = 2 * (q * THREADS + tid);
             const float w = UNI ? p.mu_uniform : 1.f;
             const float4 a0 = make_float4(w * acc.x[2 * q], w * acc.y[2 * q], w * acc.z[2 * q], 0.f);
             const float4 a1 = make_float4(w * acc.x[2 * q + 1], w * acc.y[2 * q + 1], w * acc.z[2 * q + 1], 0.f);
@@ -295,36 +346,55 @@ void build_sym_plan(const SymParams& sp, int grid, int cost_plain, int cost_sym,
 }
 
 typedef void (*SymKernel)(const SymParams);
-static int sym_npair() {       // j-pairs per lane and iteration (env GRAVSIM_SYM_NPAIR for measurements)
+static int sym_npair() {       // j-pairs per lane and iteration (GRAVSIM_SYM_NPAIR: measurement knob)
     static int v = 0;
     if (!v) { const char* e = getenv("GRAVSIM_SYM_NPAIR"); v = (e && atoi(e) == 2) ? 2 : (e && atoi(e) == 4) ? 4 : kSymDefaultNPair; }
     return v;
 }
-template <int RR, int NP>
-static SymKernel pick_sym_rn(int cut, bool uni) {
-    if (cut == kSoftened) return uni ? (SymKernel)sym_force_kernel<RR, 1, kSoftened, true, NP>
-                                     : (SymKernel)sym_force_kernel<RR, 1, kSoftened, false, NP>;
-    return uni ? (SymKernel)sym_force_kernel<RR, 1, kCutoff, true, NP> : (SymKernel)sym_force_kernel<RR, 1, kCutoff, false, NP>;
+static int sym_cut_of(int cut_mode) {
+    return cut_mode == kSoftened ? kSymSoft : cut_mode == kCutoff ? kSymSelect : kSymTrack;
 }
-static SymKernel pick_sym(int R, int cut, bool uni) {
+template <int RR, int TH, int NP>
+static SymKernel pick_sym_rn(int cut, bool uni) {
+    switch (sym_cut_of(cut)) {
+        case kSymSoft: return uni ? (SymKernel)sym_force_kernel<RR, TH, kSymSoft, true, NP> : (SymKernel)sym_force_kernel<RR, TH, kSymSoft, false, NP>;
+        case kSymSelect: return uni ? (SymKernel)sym_force_kernel<RR, TH, kSymSelect, true, NP> : (SymKernel)sym_force_kernel<RR, TH, kSymSelect, false, NP>;
+        default: return uni ? (SymKernel)sym_force_kernel<RR, TH, kSymTrack, true, NP> : (SymKernel)sym_force_kernel<RR, TH, kSymTrack, false, NP>;
+    }
+}
+// (i-bodies per thread, threads per CTA) pairs the pass is built for
+static SymKernel pick_sym(int R, int threads, int cut, bool uni) {
     const int np = sym_npair();
-    if (R == 4) return np == 4 ? pick_sym_rn<4, 4>(cut, uni) : pick_sym_rn<4, 2>(cut, uni);
-    if (R == 6) return np == 4 ? pick_sym_rn<6, 4>(cut, uni) : pick_sym_rn<6, 2>(cut, uni);
-    if (R == 8) return np == 4 ? pick_sym_rn<8, 4>(cut, uni) : pick_sym_rn<8, 2>(cut, uni);
+    if (const char* pe = getenv("GRAVSIM_SYM_PROBE")) {     // timing experiments (wrong results), headline configuration only
+        if (R == 8 && threads == 256 && cut == kSoftened && uni) {
+            if (atoi(pe) == 1) return (SymKernel)sym_force_kernel<8, 256, kSymSoft, true, 4, 1>;
+            if (atoi(pe) == 2) return (SymKernel)sym_force_kernel<8, 256, kSymSoft, true, 4, 2>;
+            if (atoi(pe) == 3) return (SymKernel)sym_force_kernel<8, 256, kSymSoft, true, 4, 3>;
+        }
+    }
+    if (threads == 256) {
+        if (R == 4) return np == 4 ? pick_sym_rn<4, 256, 4>(cut, uni) : pick_sym_rn<4, 256, 2>(cut, uni);
+        if (R == 6) return np == 4 ? pick_sym_rn<6, 256, 4>(cut, uni) : pick_sym_rn<6, 256, 2>(cut, uni);
+        if (R == 8) return np == 4 ? pick_sym_rn<8, 256, 4>(cut, uni) : pick_sym_rn<8, 256, 2>(cut, uni);
+    }
+    if (threads == 384 && R == 8) return pick_sym_rn<8, 384, 2>(cut, uni);
+    if (threads == 512 && R == 4) return np == 4 ? pick_sym_rn<4, 512, 4>(cut, uni) : pick_sym_rn<4, 512, 2>(cut, uni);
     return nullptr;
 }
 
-size_t sym_smem_bytes() { return kSymSmemBytes; }
+bool sym_supported(int R, int threads) { return pick_sym(R, threads, kSoftened, false) != nullptr; }
+size_t sym_smem_bytes(int threads) { return sym_smem_for(threads); }
 
-cudaError_t sym_kernel_setup(int R, int cut_mode, int* ctas_per_sm, int* regs) {
+cudaError_t sym_kernel_setup(int R, int threads, int cut_mode, int* ctas_per_sm, int* regs) {
     int best = 1 << 30, r = 0;
+    const size_t smem = sym_smem_for(threads);
     for (int uni = 0; uni < 2; ++uni) {
-        SymKernel k = pick_sym(R, cut_mode, uni != 0);
+        SymKernel k = pick_sym(R, threads, cut_mode, uni != 0);
         if (!k) return cudaErrorInvalidValue;
-        cudaError_t e = cudaFuncSetAttribute((const void*)k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSymSmemBytes);
+        cudaError_t e = cudaFuncSetAttribute((const void*)k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
         int n = 0;
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, (const void*)k, kSymThreads, kSymSmemBytes);
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, (const void*)k, threads, smem);
         if (e != cudaSuccess) return e;
         cudaFuncAttributes fa;
         e = cudaFuncGetAttributes(&fa, (const void*)k);
@@ -337,10 +407,10 @@ cudaError_t sym_kernel_setup(int R, int cut_mode, int* ctas_per_sm, int* regs) {
     return cudaSuccess;
 }
 
-cudaError_t launch_sym_force(int R, int cut_mode, const SymParams& p, int grid, cudaStream_t s) {
-    SymKernel k = pick_sym(R, cut_mode, p.mu_uniform != 0.f);
+cudaError_t launch_sym_force(int R, int threads, int cut_mode, const SymParams& p, int grid, cudaStream_t s) {
+    SymKernel k = pick_sym(R, threads, cut_mode, p.mu_uniform != 0.f);
     if (!k) return cudaErrorInvalidValue;
-    k<<<grid, kSymThreads, kSymSmemBytes, s>>>(p);
+    k<<<grid, threads, sym_smem_for(threads), s>>>(p);
     return cudaGetLastError();
 }
 

@@ -66,12 +66,10 @@ typedef struct gs_config {
     int32_t  variant;       /* kernel variant; 0 = default (see gs_info.variant)                 */
 } gs_config;
 
-#define GS_FLAG_NO_OVERLAP 1u   /* (default behaviour; kept for callers that set it) one force pass per step    */
 #define GS_FLAG_TWO_PASS   2u   /* one GPU: run the multi-GPU local-then-remote two-pass schedule  */
 #define GS_FLAG_NO_UNIFORM_MASS 4u /* keep the general kernel even when all masses are equal        */
 #define GS_FLAG_OVERLAP    8u   /* multi-GPU: own j-slice first, remote slices after the exchange  */
 #define GS_FLAG_NCCL_EXCHANGE 16u /* multi-GPU: per-step ncclAllGather instead of peer-memory stores */
-#define GS_FLAG_SYMMETRIC  64u   /* (default behaviour; kept for callers that set it) pair-symmetric force pass   */
 #define GS_FLAG_DETERMINISTIC 128u /* bit-reproducible sums: use the row-gather kernel instead of the default
                                    pair-symmetric pass (every unordered pair once, applied to both bodies as
                                    cuda.cu:43-49 does -- ~1.3x faster, but its floating-point atomics make the

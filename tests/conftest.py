@@ -167,6 +167,13 @@ def reference():
     return Reference()
 
 
+def floor_err(a, ref, normsum):
+    """per-body |a - ref| / max(|ref|, 1e-3 * sum_j |a_ij|): the relative error with the floor SURVEY.md section 7
+    asks for where |a_i| is a near-total cancellation (centre of a Plummer sphere).  Compared with 1e-5."""
+    num = np.linalg.norm(np.asarray(a, dtype=np.float64) - ref, axis=1)
+    return num / np.maximum(np.linalg.norm(ref, axis=1), 1e-3 * normsum)
+
+
 def rel_err(a, ref):
     """per-body |a - ref| / |ref| (3-vectors)."""
     num = np.linalg.norm(np.asarray(a, dtype=np.float64) - ref, axis=1)
