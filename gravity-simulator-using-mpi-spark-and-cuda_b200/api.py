@@ -29,6 +29,7 @@ NCCL_ID_BYTES = 128
 EXPORTED_SYMBOLS = [
     "gs_config_init", "gs_create", "gs_destroy", "gs_nccl_unique_id",
     "gs_upload_aos_f32", "gs_upload_aos_f64", "gs_download_aos_f32", "gs_download_aos_f64",
+    "gs_upload_slice_f32", "gs_upload_slice_f64", "gs_download_slice_f32", "gs_download_slice_f64",
     "gs_step", "gs_step_trajectory", "gs_accel", "gs_energy", "gs_potential_energy_noalloc", "gs_sync", "gs_set_dt",
     "gs_get_info", "gs_kernel_launches", "gs_last_cuda_error", "gs_strerror", "gs_version",
     "gs_host_alloc", "gs_host_free",
@@ -117,6 +118,8 @@ def lib():
     L.gs_destroy.restype = None
     for f in ("gs_upload_aos_f32", "gs_upload_aos_f64", "gs_download_aos_f32", "gs_download_aos_f64"):
         getattr(L, f).argtypes = [C.c_void_p, C.c_void_p, C.c_int]
+    for f in ("gs_upload_slice_f32", "gs_upload_slice_f64", "gs_download_slice_f32", "gs_download_slice_f64"):
+        getattr(L, f).argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int]
     L.gs_step.argtypes = [C.c_void_p, C.c_int]
     L.gs_step_trajectory.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.POINTER(C.c_int)]
     L.gs_accel.argtypes = [C.c_void_p, C.c_void_p]
@@ -343,6 +346,33 @@ class GravSim:
     def download_ptr(self, ptr, n, record_bytes=28):
         fn = lib().gs_download_aos_f32 if record_bytes == 28 else lib().gs_download_aos_f64
         _check(fn(self._ctx, C.c_void_p(ptr), n), "gs_download_aos", self._ctx)
+
+    # -- this rank's own records only (mpi.c:184-187's slice)
+    @property
+    def my_range(self):
+        return self.info.i_begin, self.info.i_end
+
+    def upload_slice(self, my_particles):
+        """Collective: every rank passes the records of ITS bodies [i_begin, i_end) only."""
+        a = np.asarray(my_particles)
+        dt = np.float64 if a.dtype == np.float64 else np.float32
+        r = np.ascontiguousarray(a, dtype=dt).reshape(-1, 7)
+        self.upload_slice_ptr(r.ctypes.data, r.shape[0], 56 if dt == np.float64 else 28)
+
+    def upload_slice_ptr(self, ptr, count, record_bytes=28):
+        fn = lib().gs_upload_slice_f32 if record_bytes == 28 else lib().gs_upload_slice_f64
+        _check(fn(self._ctx, C.c_void_p(ptr), self.info.i_begin, count), "gs_upload_slice", self._ctx)
+        lib().gs_get_info(self._ctx, C.byref(self.info))
+
+    def download_slice(self, dtype=np.float32):
+        lo, hi = self.my_range
+        out = np.empty((max(hi - lo, 0), 7), dtype=dtype)
+        self.download_slice_ptr(out.ctypes.data, out.shape[0], 28 if dtype == np.float32 else 56)
+        return out
+
+    def download_slice_ptr(self, ptr, count, record_bytes=28):
+        fn = lib().gs_download_slice_f32 if record_bytes == 28 else lib().gs_download_slice_f64
+        _check(fn(self._ctx, C.c_void_p(ptr), self.info.i_begin, count), "gs_download_slice", self._ctx)
 
     # -- hot path
     def step(self, nsteps=1):

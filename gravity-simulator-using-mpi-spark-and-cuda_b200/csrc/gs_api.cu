@@ -39,7 +39,10 @@ struct gs_ctx {
     float4* acc_out = nullptr;    // gs_accel output (lazy)
     float4* partial = nullptr;    // split-tile scratch
     size_t partial_bytes = 0;
-    double* mass = nullptr;
+    double* mass = nullptr;       // n_pad doubles: original masses (returned bit-exactly by downloads)
+    bool mass_full = true;        // false after a slice upload: only this rank's part of mass[] is valid
+    uint32_t* d_mu_mm = nullptr;  // {min, max} bit pattern of mu over the uploaded bodies (equal-mass detection on the device)
+    uint32_t* h_mu_mm = nullptr;  // pinned mirror (2 words) + 2 words of presets
     void* d_aos = nullptr;        // staging for the reference-layout records
     size_t d_aos_bytes = 0;
     double* d_energy = nullptr;   // per-CTA partials: [egrid] potential + [egrid*4] kinetic/momentum + 8
@@ -444,6 +447,16 @@ int set_device(gs_ctx* c) {
     return GS_OK;
 }
 
+// In peer-memory mode a wait kernel that gave up on a lost peer only leaves a mark: turn it into an error code
+// after every host synchronisation, so that no entry point hands back data computed from stale peer positions.
+int check_peers(gs_ctx* c) {
+    if (!c->p2p) return GS_OK;
+    uint32_t err = 0;
+    GS_CUDA(c, cudaMemcpy(&err, c->d_comm_err, sizeof(err), cudaMemcpyDeviceToHost));
+    return err ? GS_ENCCL : GS_OK;
+}
+
+
 }  // namespace
 
 extern "C" {
@@ -602,8 +615,9 @@ void gs_destroy(gs_ctx* c) {
     cudaFree(c->d_sym_ctas); cudaFree(c->d_sym_rows); cudaFree(c->d_accj); cudaFree(c->sym_partial);
     cudaFree(c->pos_lo); cudaFree(c->vel_lo); cudaFree(c->lo_full[0]); cudaFree(c->lo_full[1]);
     cudaFree(c->acc_local); cudaFree(c->acc_stage); cudaFree(c->acc_out); cudaFree(c->partial); cudaFree(c->mass);
-    cudaFree(c->d_aos); cudaFree(c->d_energy);
+    cudaFree(c->d_aos); cudaFree(c->d_energy); cudaFree(c->d_mu_mm);
     if (c->h_energy) cudaFreeHost(c->h_energy);
+    if (c->h_mu_mm) cudaFreeHost(c->h_mu_mm);
     if (c->h_acc) cudaFreeHost(c->h_acc);
     if (c->ev_integ) cudaEventDestroy(c->ev_integ);
     for (int b = 0; b < 2; ++b)
@@ -738,6 +752,10 @@ int gs_create(gs_ctx** out, const gs_config* cfg) {
     if (cudaHostAlloc((void**)&c->h_energy, ((size_t)egrid * 5 + 8) * sizeof(double), cudaHostAllocDefault) !=
         cudaSuccess)
         return fail(GS_ENOMEM);
+    if (!dmalloc((void**)&c->d_mu_mm, 4 * sizeof(uint32_t)) ||
+        cudaHostAlloc((void**)&c->h_mu_mm, 4 * sizeof(uint32_t), cudaHostAllocDefault) != cudaSuccess)
+        return fail(GS_ENOMEM);
+    c->h_mu_mm[2] = 0xffffffffu; c->h_mu_mm[3] = 0u;      // presets of {min, max}
 
     if (cfg->stream) { c->stream = (cudaStream_t)cfg->stream; c->own_stream = false; }
     else {
@@ -762,6 +780,34 @@ int gs_create(gs_ctx** out, const gs_config* cfg) {
     return GS_OK;
 }
 
+// Are all uploaded masses equal?  Decided from the {min, max} bit patterns of mu the upload kernel left in
+// d_mu_mm (on several GPUs after a slice upload: min over ranks of {min, ~max}).  Needs the value on the host because
+// it picks the kernel (mass factor hoisted out of the inner loop), hence one 8-byte D2H and a stream synchronisation.
+static int decide_uniform_mass(gs_ctx* c, bool reduce_over_ranks) {
+    c->mu_uniform = 0.f;
+    if (c->cfg.flags & GS_FLAG_NO_UNIFORM_MASS) return GS_OK;
+    if (reduce_over_ranks && c->cfg.world_size > 1) {
+        if (nccl_api().AllReduce(c->d_mu_mm + 2, c->d_mu_mm + 2, 2, ncclUint32, ncclMin, c->comm, c->stream) != ncclSuccess)
+            return GS_ENCCL;
+    }
+    GS_CUDA(c, cudaMemcpyAsync(c->h_mu_mm, c->d_mu_mm + 2, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+    GS_CUDA(c, cudaStreamSynchronize(c->stream));
+    const uint32_t lo = c->h_mu_mm[0], hi = ~c->h_mu_mm[1];
+    float mu;
+    memcpy(&mu, &lo, 4);
+    if (lo == hi && mu > 0.f && std::isfinite(mu)) c->mu_uniform = mu;
+    return GS_OK;
+}
+
+static int reset_after_upload(gs_ctx* c) {
+    if (c->copy_stream) GS_CUDA(c, cudaStreamSynchronize(c->copy_stream));
+    c->buf_copy_pending[0] = c->buf_copy_pending[1] = false;
+    c->uploaded = true;
+    c->vel_synced = true;
+    c->steps_done = 0;
+    return GS_OK;
+}
+
 static int upload_common(gs_ctx* c, const void* host, int n, int record_bytes) {
     if (!c || !host) return GS_EINVAL;
     if (n != c->n) return GS_EINVAL;
@@ -770,34 +816,17 @@ static int upload_common(gs_ctx* c, const void* host, int n, int record_bytes) {
     const size_t bytes = (size_t)n * record_bytes;
     if ((rc = ensure_aos(c, bytes)) != GS_OK) return rc;
     GS_CUDA(c, cudaMemcpyAsync(c->d_aos, host, bytes, cudaMemcpyHostToDevice, c->stream));
-    // equal masses (Plummer spheres, cosmological particles): the mass factor leaves the inner loop
-    c->mu_uniform = 0.f;
-    if (!(c->cfg.flags & GS_FLAG_NO_UNIFORM_MASS)) {
-        bool same = true;
-        double m0;
-        if (record_bytes == 28) {
-            const char* b = (const char*)host;
-            float f0, f;
-            memcpy(&f0, b + 24, 4);
-            for (int i = 1; i < n && same; ++i) { memcpy(&f, b + (size_t)i * 28 + 24, 4); same = (f == f0); }
-            m0 = f0;
-        } else {
-            const double* d = (const double*)host;
-            m0 = d[6];
-            for (int i = 1; i < n && same; ++i) same = (d[(size_t)i * 7 + 6] == m0);
-        }
-        const float mu = (float)(c->cfg.G * m0);
-        if (same && mu > 0.f && std::isfinite(mu)) c->mu_uniform = mu;
-    }
+    GS_CUDA(c, cudaMemcpyAsync(c->d_mu_mm, c->h_mu_mm + 2, 2 * sizeof(uint32_t), cudaMemcpyHostToDevice, c->stream));
     c->cur = 0;
-    GS_CUDA(c, launch_aos_to_packed(c->d_aos, record_bytes, n, c->n_pad, c->cfg.G, c->pos[0], c->vel, c->mass,
-                                    c->i_begin, c->slice, c->pos_lo, c->vel_lo, c->stream));
-    c->launches++;
-    // the other buffer must carry mu and the padding too: remote slices are filled by the exchange,
-    // the own slice by the integrator, but the padding bodies of a single-GPU run are only ever
-    // written here.
-    GS_CUDA(c, cudaMemcpyAsync(c->pos[1], c->pos[0], (size_t)c->n_pad * sizeof(float4), cudaMemcpyDeviceToDevice,
-                               c->stream));
+    // both buffers must carry mu and the padding: remote slices are filled by the exchange, the own slice by the
+    // integrator, but the padding bodies of a single-GPU run are only ever written here
+    UploadTargets dst;
+    dst.n = 2; dst.pos[0] = c->pos[0]; dst.pos[1] = c->pos[1];
+    GS_CUDA(c, launch_aos_to_packed(c->d_aos, record_bytes, 0, n, 0, c->n_pad, c->cfg.G, dst, c->vel, c->mass, c->i_begin,
+                                    c->slice, c->pos_lo, c->vel_lo, c->d_mu_mm, c->stream));
+    GS_CUDA(c, launch_pack_minmax(c->d_mu_mm, c->stream));
+    c->launches += 2;
+    c->mass_full = true;
     if (c->cfg.world_size > 1) {
         // every rank uploaded the full array: pos[0] is already complete everywhere.
         if (c->p2p) {
@@ -810,16 +839,67 @@ static int upload_common(gs_ctx* c, const void* host, int n, int record_bytes) {
             GS_CUDA(c, cudaEventRecord(c->ev_gather[0], c->comm_stream));
         }
     }
-    if (c->copy_stream) GS_CUDA(c, cudaStreamSynchronize(c->copy_stream));
-    c->buf_copy_pending[0] = c->buf_copy_pending[1] = false;
-    c->uploaded = true;
-    c->vel_synced = true;
-    c->steps_done = 0;
-    return GS_OK;
+    if ((rc = decide_uniform_mass(c, false)) != GS_OK) return rc;     // every rank saw every mass
+    return reset_after_upload(c);
 }
 
 int gs_upload_aos_f32(gs_ctx* ctx, const void* particles28, int n) { return upload_common(ctx, particles28, n, 28); }
 int gs_upload_aos_f64(gs_ctx* ctx, const void* particles56, int n) { return upload_common(ctx, particles56, n, 56); }
+
+// A rank uploads only the records of its own i-bodies (mpi.c:184-187: rank r owns [start_idx, start_idx + local_n));
+// the packed positions reach the other GPUs over NVLink instead of every rank pushing the whole array through PCIe.
+static int upload_slice_common(gs_ctx* c, const void* host, int first, int count, int record_bytes) {
+    if (!c || (!host && count > 0)) return GS_EINVAL;
+    const int lo = c->i_begin < c->n ? c->i_begin : c->n;
+    const int hi = (c->i_begin + c->slice) < c->n ? (c->i_begin + c->slice) : c->n;
+    if (first != lo || count != hi - lo) return GS_EINVAL;
+    int rc = set_device(c);
+    if (rc != GS_OK) return rc;
+    const int W = c->cfg.world_size;
+    const size_t bytes = (size_t)count * record_bytes;
+    if (count > 0) {
+        if ((rc = ensure_aos(c, bytes)) != GS_OK) return rc;
+        GS_CUDA(c, cudaMemcpyAsync(c->d_aos, host, bytes, cudaMemcpyHostToDevice, c->stream));
+    }
+    GS_CUDA(c, cudaMemcpyAsync(c->d_mu_mm, c->h_mu_mm + 2, 2 * sizeof(uint32_t), cudaMemcpyHostToDevice, c->stream));
+    c->cur = 0;
+    UploadTargets dst;
+    dst.n = 0;
+    if (W > 1 && c->p2p) {
+        // Epoch 1: nobody stores into a peer before that peer's stream is past everything that read its buffers
+        // (a gs_accel / gs_energy after the last step); epoch 2 (below): the stores have landed everywhere.
+        if ((rc = wait_positions(c)) != GS_OK) return rc;
+        if ((rc = exchange_positions(c, 0)) != GS_OK) return rc;
+        if ((rc = wait_positions(c)) != GS_OK) return rc;
+        for (int q = 0; q < W; ++q) { dst.pos[dst.n++] = c->peer_pos[0][q]; dst.pos[dst.n++] = c->peer_pos[1][q]; }
+    } else {
+        dst.pos[dst.n++] = c->pos[0];
+        dst.pos[dst.n++] = c->pos[1];
+    }
+    GS_CUDA(c, launch_aos_to_packed(c->d_aos, record_bytes, first, c->n, c->i_begin, c->slice, c->cfg.G, dst, c->vel,
+                                    c->mass, c->i_begin, c->slice, c->pos_lo, c->vel_lo, c->d_mu_mm, c->stream));
+    GS_CUDA(c, launch_pack_minmax(c->d_mu_mm, c->stream));
+    c->launches += 2;
+    c->mass_full = (W == 1);
+    if (W > 1) {
+        if (c->p2p) {
+            if ((rc = exchange_positions(c, 0)) != GS_OK) return rc;
+        } else {        // no peer access: in-place all-gather of both buffers
+            NcclApi& nc = nccl_api();
+            for (int b = 0; b < 2; ++b)
+                if (nc.AllGather(c->pos[b] + c->i_begin, c->pos[b], (size_t)c->slice * 4, ncclFloat, c->comm, c->stream) != ncclSuccess)
+                    return GS_ENCCL;
+            GS_CUDA(c, cudaEventRecord(c->ev_integ, c->stream));
+            GS_CUDA(c, cudaStreamWaitEvent(c->comm_stream, c->ev_integ, 0));
+            GS_CUDA(c, cudaEventRecord(c->ev_gather[0], c->comm_stream));
+        }
+    }
+    if ((rc = decide_uniform_mass(c, true)) != GS_OK) return rc;
+    return reset_after_upload(c);
+}
+
+int gs_upload_slice_f32(gs_ctx* ctx, const void* my28, int first, int count) { return upload_slice_common(ctx, my28, first, count, 28); }
+int gs_upload_slice_f64(gs_ctx* ctx, const void* my56, int first, int count) { return upload_slice_common(ctx, my56, first, count, 56); }
 
 static int one_step(gs_ctx* c) {
     int rc;
@@ -910,7 +990,7 @@ int gs_step_trajectory(gs_ctx* c, int nsteps, int every, float* xyz_host, int ca
     }
     if (c->cfg.world_size > 1 && nsteps > 0 && (rc = wait_positions(c)) != GS_OK) return rc;
     if (n_snapshots) *n_snapshots = taken;
-    return GS_OK;
+    return taken > 0 ? check_peers(c) : GS_OK;        // the frames were synchronised above
 }
 
 int gs_accel(gs_ctx* c, float* acc3_host) {
@@ -933,6 +1013,7 @@ int gs_accel(gs_ctx* c, float* acc3_host) {
     GS_CUDA(c, cudaMemcpyAsync(c->h_acc, c->acc_out, (size_t)n_local * sizeof(float4), cudaMemcpyDeviceToHost,
                                c->stream));
     GS_CUDA(c, cudaStreamSynchronize(c->stream));
+    if ((rc = check_peers(c)) != GS_OK) return rc;
     for (int i = 0; i < n_local; ++i) {
         acc3_host[3 * (size_t)i + 0] = c->h_acc[i].x;
         acc3_host[3 * (size_t)i + 1] = c->h_acc[i].y;
@@ -958,6 +1039,7 @@ int gs_energy(gs_ctx* c, double* kinetic, double* potential, double momentum[3])
     GS_CUDA(c, cudaMemcpyAsync(c->h_energy, c->d_energy, (size_t)egrid * 5 * sizeof(double), cudaMemcpyDeviceToHost,
                                c->stream));
     GS_CUDA(c, cudaStreamSynchronize(c->stream));
+    if ((rc = check_peers(c)) != GS_OK) return rc;
     double v[5] = {0, 0, 0, 0, 0};   // {sum mu_i phi_i, sum m v^2, px, py, pz}
     for (int b = 0; b < egrid; ++b) {
         v[0] += c->h_energy[b];
@@ -996,6 +1078,11 @@ static int download_common(gs_ctx* c, void* host, int n, int record_bytes) {
         if (nc.AllGather(c->vel, c->vel_full, (size_t)c->slice * 4, ncclFloat, c->comm, c->stream) != ncclSuccess)
             return GS_ENCCL;
         vel_full = c->vel_full;
+        if (!c->mass_full) {     // after a slice upload every rank only holds its own masses
+            if (nc.AllGather(c->mass + c->i_begin, c->mass, (size_t)c->slice, ncclDouble, c->comm, c->stream) != ncclSuccess)
+                return GS_ENCCL;
+            c->mass_full = true;
+        }
         if (c->pos_lo) {
             const float4* src[2] = {c->pos_lo, c->vel_lo};
             for (int k = 0; k < 2; ++k) {
@@ -1008,16 +1095,41 @@ static int download_common(gs_ctx* c, void* host, int n, int record_bytes) {
     }
     const size_t bytes = (size_t)n * record_bytes;
     if ((rc = ensure_aos(c, bytes)) != GS_OK) return rc;
-    GS_CUDA(c, launch_packed_to_aos(c->pos[c->cur], vel_full, c->mass, n, c->d_aos, record_bytes, pos_lo_full,
+    GS_CUDA(c, launch_packed_to_aos(c->pos[c->cur], vel_full, 0, c->mass, 0, n, c->d_aos, record_bytes, pos_lo_full,
                                     vel_lo_full, c->stream));
     c->launches++;
     GS_CUDA(c, cudaMemcpyAsync(host, c->d_aos, bytes, cudaMemcpyDeviceToHost, c->stream));
     GS_CUDA(c, cudaStreamSynchronize(c->stream));
-    return GS_OK;
+    return check_peers(c);
 }
 
 int gs_download_aos_f32(gs_ctx* ctx, void* particles28, int n) { return download_common(ctx, particles28, n, 28); }
 int gs_download_aos_f64(gs_ctx* ctx, void* particles56, int n) { return download_common(ctx, particles56, n, 56); }
+
+// This rank's own records only: nothing crosses between GPUs (positions, velocities and masses of the slice are local).
+static int download_slice_common(gs_ctx* c, void* host, int first, int count, int record_bytes) {
+    if (!c || (!host && count > 0)) return GS_EINVAL;
+    if (!c->uploaded) return GS_ESTATE;
+    const int lo = c->i_begin < c->n ? c->i_begin : c->n;
+    const int hi = (c->i_begin + c->slice) < c->n ? (c->i_begin + c->slice) : c->n;
+    if (first != lo || count != hi - lo) return GS_EINVAL;
+    int rc = set_device(c);
+    if (rc != GS_OK) return rc;
+    if ((rc = sync_velocities(c)) != GS_OK) return rc;       // collective with GS_INTEGRATOR_LEAPFROG
+    if (count > 0) {
+        const size_t bytes = (size_t)count * record_bytes;
+        if ((rc = ensure_aos(c, bytes)) != GS_OK) return rc;
+        GS_CUDA(c, launch_packed_to_aos(c->pos[c->cur], c->vel, c->i_begin, c->mass, c->i_begin, count, c->d_aos,
+                                        record_bytes, c->pos_lo, c->vel_lo, c->stream));
+        c->launches++;
+        GS_CUDA(c, cudaMemcpyAsync(host, c->d_aos, bytes, cudaMemcpyDeviceToHost, c->stream));
+    }
+    GS_CUDA(c, cudaStreamSynchronize(c->stream));
+    return check_peers(c);
+}
+
+int gs_download_slice_f32(gs_ctx* ctx, void* my28, int first, int count) { return download_slice_common(ctx, my28, first, count, 28); }
+int gs_download_slice_f64(gs_ctx* ctx, void* my56, int first, int count) { return download_slice_common(ctx, my56, first, count, 56); }
 
 int gs_sync(gs_ctx* c) {
     if (!c) return GS_EINVAL;
@@ -1025,12 +1137,7 @@ int gs_sync(gs_ctx* c) {
     if (rc != GS_OK) return rc;
     GS_CUDA(c, cudaStreamSynchronize(c->stream));
     if (c->comm_stream) GS_CUDA(c, cudaStreamSynchronize(c->comm_stream));
-    if (c->p2p) {      // a peer never raised its flag: the wait kernel gave up instead of hanging the GPU
-        uint32_t err = 0;
-        GS_CUDA(c, cudaMemcpy(&err, c->d_comm_err, sizeof(err), cudaMemcpyDeviceToHost));
-        if (err) return GS_ENCCL;
-    }
-    return GS_OK;
+    return check_peers(c);      // a peer never raised its flag: the wait kernel gave up instead of hanging the GPU
 }
 
 int gs_set_dt(gs_ctx* c, double dt) {

@@ -296,98 +296,125 @@ cudaError_t launch_wait_flags(const uint32_t* my_flags, int world, int my_rank, 
 // ------------------------------------------------------------------------------------------------
 // AoS <-> packed pairs
 // ------------------------------------------------------------------------------------------------
+// Bodies [body_first, body_first + body_count) (even bounds): the record of body i is aos[(i - rec_first) * 7];
+// bodies >= n are padding.  Packed positions go to every buffer in `dst` (full upload: this GPU's two buffers;
+// slice upload: both buffers of every GPU, over NVLink), velocities / masses / low-order words stay local.
+// mu_minmax[0] = min, mu_minmax[1] = max over the real bodies of the bit pattern of mu: equal <=> all masses equal.
 template <typename T>
-__global__ void aos_to_packed_kernel(const T* __restrict__ aos, int n, int n_pad, double G, float4* pos,
-                                     float4* vel_local, double* mass, int i_begin, int n_local_pad,
-                                     float4* pos_lo_local, float4* vel_lo_local) {
-    const int pair = blockIdx.x * blockDim.x + threadIdx.x;
-    if (pair >= n_pad / 2) return;
-    float x[2], y[2], z[2], vx[2], vy[2], vz[2], mu[2];
-    float lo[2][6];
+__global__ void aos_to_packed_kernel(const T* __restrict__ aos, int rec_first, int n, int body_first, int body_count,
+                                     double G, UploadTargets dst, float4* vel_local, double* mass, int i_begin,
+                                     int n_local_pad, float4* pos_lo_local, float4* vel_lo_local, uint32_t* mu_minmax) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t lo_bits = 0xffffffffu, hi_bits = 0u;
+    if (k < body_count / 2) {
+        const int pair = (body_first >> 1) + k;
+        float x[2], y[2], z[2], vx[2], vy[2], vz[2], mu[2];
+        float lo[2][6];
 #pragma unroll
-    for (int h = 0; h < 2; ++h) {
-        const int i = 2 * pair + h;
-        if (i < n) {
-            const T* r = aos + (size_t)i * 7;
-            x[h] = (float)r[0]; y[h] = (float)r[1]; z[h] = (float)r[2];
-            vx[h] = (float)r[3]; vy[h] = (float)r[4]; vz[h] = (float)r[5];
-            const float hi[6] = {x[h], y[h], z[h], vx[h], vy[h], vz[h]};
+        for (int h = 0; h < 2; ++h) {
+            const int i = 2 * pair + h;
+            if (i < n) {
+                const T* r = aos + (size_t)(i - rec_first) * 7;
+                x[h] = (float)r[0]; y[h] = (float)r[1]; z[h] = (float)r[2];
+                vx[h] = (float)r[3]; vy[h] = (float)r[4]; vz[h] = (float)r[5];
+                const float hi[6] = {x[h], y[h], z[h], vx[h], vy[h], vz[h]};
 #pragma unroll
-            for (int c = 0; c < 6; ++c) lo[h][c] = (float)((double)r[c] - (double)hi[c]);   // 0 for f32 records
-            const double m = (double)r[6];
-            mu[h] = (float)(G * m);          // never form m_i*m_j: G*m <= 1.33e20 fits fp32
-            mass[i] = m;
-        } else {                             // padding: massless, at rest, so far away that rinv^3 underflows to 0
-            x[h] = y[h] = z[h] = kPadPosition;
-            vx[h] = vy[h] = vz[h] = mu[h] = 0.f;
+                for (int c = 0; c < 6; ++c) lo[h][c] = (float)((double)r[c] - (double)hi[c]);   // 0 for f32 records
+                const double m = (double)r[6];
+                mu[h] = (float)(G * m);          // never form m_i*m_j: G*m <= 1.33e20 fits fp32
+                mass[i] = m;
+                const uint32_t bits = __float_as_uint(mu[h]);
+                lo_bits = min(lo_bits, bits); hi_bits = max(hi_bits, bits);
+            } else {                             // padding: massless, at rest, so far away that rinv^3 underflows to 0
+                x[h] = y[h] = z[h] = kPadPosition;
+                vx[h] = vy[h] = vz[h] = mu[h] = 0.f;
 #pragma unroll
-            for (int c = 0; c < 6; ++c) lo[h][c] = 0.f;
-            mass[i] = 0.0;
+                for (int c = 0; c < 6; ++c) lo[h][c] = 0.f;
+                mass[i] = 0.0;
+            }
+        }
+        const float4 PA = make_float4(x[0], x[1], y[0], y[1]), PB = make_float4(z[0], z[1], mu[0], mu[1]);
+        for (int q = 0; q < dst.n; ++q) { dst.pos[q][2 * pair] = PA; dst.pos[q][2 * pair + 1] = PB; }
+        const int first = 2 * pair;
+        if (first >= i_begin && first < i_begin + n_local_pad) {
+            const int pl = (first - i_begin) >> 1;
+            vel_local[2 * pl] = make_float4(vx[0], vx[1], vy[0], vy[1]);
+            vel_local[2 * pl + 1] = make_float4(vz[0], vz[1], 0.f, 0.f);
+            if (pos_lo_local != nullptr) {
+                pos_lo_local[2 * pl] = make_float4(lo[0][0], lo[1][0], lo[0][1], lo[1][1]);
+                pos_lo_local[2 * pl + 1] = make_float4(lo[0][2], lo[1][2], 0.f, 0.f);
+                vel_lo_local[2 * pl] = make_float4(lo[0][3], lo[1][3], lo[0][4], lo[1][4]);
+                vel_lo_local[2 * pl + 1] = make_float4(lo[0][5], lo[1][5], 0.f, 0.f);
+            }
         }
     }
-    pos[2 * pair] = make_float4(x[0], x[1], y[0], y[1]);
-    pos[2 * pair + 1] = make_float4(z[0], z[1], mu[0], mu[1]);
-    const int first = 2 * pair;
-    if (first >= i_begin && first < i_begin + n_local_pad) {
-        const int pl = (first - i_begin) >> 1;
-        vel_local[2 * pl] = make_float4(vx[0], vx[1], vy[0], vy[1]);
-        vel_local[2 * pl + 1] = make_float4(vz[0], vz[1], 0.f, 0.f);
-        if (pos_lo_local != nullptr) {
-            pos_lo_local[2 * pl] = make_float4(lo[0][0], lo[1][0], lo[0][1], lo[1][1]);
-            pos_lo_local[2 * pl + 1] = make_float4(lo[0][2], lo[1][2], 0.f, 0.f);
-            vel_lo_local[2 * pl] = make_float4(lo[0][3], lo[1][3], lo[0][4], lo[1][4]);
-            vel_lo_local[2 * pl + 1] = make_float4(lo[0][5], lo[1][5], 0.f, 0.f);
-        }
-    }
+    lo_bits = __reduce_min_sync(0xffffffffu, lo_bits);
+    hi_bits = __reduce_max_sync(0xffffffffu, hi_bits);
+    if ((threadIdx.x & 31) == 0 && lo_bits <= hi_bits) { atomicMin(mu_minmax, lo_bits); atomicMax(mu_minmax + 1, hi_bits); }
 }
 
+// Bodies [body_first, body_first + count): pos is indexed globally, vel / lo words with (body - vel_first),
+// records are written to aos[(body - body_first) * 7].
 template <typename T>
-__global__ void packed_to_aos_kernel(const float4* __restrict__ pos, const float4* __restrict__ vel,
-                                     const double* __restrict__ mass, int n, T* aos,
+__global__ void packed_to_aos_kernel(const float4* __restrict__ pos, const float4* __restrict__ vel, int vel_first,
+                                     const double* __restrict__ mass, int body_first, int count, T* aos,
                                      const float4* __restrict__ pos_lo, const float4* __restrict__ vel_lo) {
-    const int pair = blockIdx.x * blockDim.x + threadIdx.x;
-    if (2 * pair >= n) return;
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (2 * k >= count) return;
+    const int pair = (body_first >> 1) + k, vp = pair - (vel_first >> 1);
     const float4 PA = pos[2 * pair], PB = pos[2 * pair + 1];
-    const float4 VA = vel[2 * pair], VB = vel[2 * pair + 1];
+    const float4 VA = vel[2 * vp], VB = vel[2 * vp + 1];
     float4 LA = make_float4(0.f, 0.f, 0.f, 0.f), LB = LA, WA = LA, WB = LA;
-    if (pos_lo != nullptr) { LA = pos_lo[2 * pair]; LB = pos_lo[2 * pair + 1]; WA = vel_lo[2 * pair]; WB = vel_lo[2 * pair + 1]; }
+    if (pos_lo != nullptr) { LA = pos_lo[2 * vp]; LB = pos_lo[2 * vp + 1]; WA = vel_lo[2 * vp]; WB = vel_lo[2 * vp + 1]; }
     {
-        T* r = aos + (size_t)(2 * pair) * 7;
+        T* r = aos + (size_t)(2 * k) * 7;
         r[0] = (T)((double)PA.x + LA.x); r[1] = (T)((double)PA.z + LA.z); r[2] = (T)((double)PB.x + LB.x);
         r[3] = (T)((double)VA.x + WA.x); r[4] = (T)((double)VA.z + WA.z); r[5] = (T)((double)VB.x + WB.x);
         r[6] = (T)mass[2 * pair];
     }
-    if (2 * pair + 1 < n) {
-        T* r = aos + (size_t)(2 * pair + 1) * 7;
+    if (2 * k + 1 < count) {
+        T* r = aos + (size_t)(2 * k + 1) * 7;
         r[0] = (T)((double)PA.y + LA.y); r[1] = (T)((double)PA.w + LA.w); r[2] = (T)((double)PB.y + LB.y);
         r[3] = (T)((double)VA.y + WA.y); r[4] = (T)((double)VA.w + WA.w); r[5] = (T)((double)VB.y + WB.y);
         r[6] = (T)mass[2 * pair + 1];
     }
 }
 
-cudaError_t launch_aos_to_packed(const void* aos, int record_bytes, int n, int n_pad, double G, float4* pos,
-                                 float4* vel_local, double* mass, int i_begin, int n_local_pad,
-                                 float4* pos_lo_local, float4* vel_lo_local, cudaStream_t s) {
-    const int blocks = (n_pad / 2 + 255) / 256;
+// {min, max} -> {min, ~max} behind them, so that ONE min-reduction over ranks gives both
+__global__ void pack_minmax_kernel(uint32_t* mm) { mm[2] = mm[0]; mm[3] = ~mm[1]; }
+cudaError_t launch_pack_minmax(uint32_t* mm4, cudaStream_t s) {
+    pack_minmax_kernel<<<1, 1, 0, s>>>(mm4);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_aos_to_packed(const void* aos, int record_bytes, int rec_first, int n, int body_first,
+                                 int body_count, double G, const UploadTargets& dst, float4* vel_local, double* mass,
+                                 int i_begin, int n_local_pad, float4* pos_lo_local, float4* vel_lo_local,
+                                 uint32_t* mu_minmax, cudaStream_t s) {
+    const int blocks = (body_count / 2 + 255) / 256;
+    if (blocks <= 0) return cudaErrorInvalidValue;
     if (record_bytes == 28)
-        aos_to_packed_kernel<float><<<blocks, 256, 0, s>>>((const float*)aos, n, n_pad, G, pos, vel_local, mass,
-                                                           i_begin, n_local_pad, pos_lo_local, vel_lo_local);
+        aos_to_packed_kernel<float><<<blocks, 256, 0, s>>>((const float*)aos, rec_first, n, body_first, body_count, G, dst,
+                                                           vel_local, mass, i_begin, n_local_pad, pos_lo_local,
+                                                           vel_lo_local, mu_minmax);
     else if (record_bytes == 56)
-        aos_to_packed_kernel<double><<<blocks, 256, 0, s>>>((const double*)aos, n, n_pad, G, pos, vel_local, mass,
-                                                            i_begin, n_local_pad, pos_lo_local, vel_lo_local);
+        aos_to_packed_kernel<double><<<blocks, 256, 0, s>>>((const double*)aos, rec_first, n, body_first, body_count, G,
+                                                            dst, vel_local, mass, i_begin, n_local_pad, pos_lo_local,
+                                                            vel_lo_local, mu_minmax);
     else
         return cudaErrorInvalidValue;
     return cudaGetLastError();
 }
 
-cudaError_t launch_packed_to_aos(const float4* pos, const float4* vel_full, const double* mass, int n, void* aos,
-                                 int record_bytes, const float4* pos_lo_full, const float4* vel_lo_full,
-                                 cudaStream_t s) {
-    const int blocks = ((n + 1) / 2 + 255) / 256;
+cudaError_t launch_packed_to_aos(const float4* pos, const float4* vel, int vel_first, const double* mass,
+                                 int body_first, int count, void* aos, int record_bytes, const float4* pos_lo,
+                                 const float4* vel_lo, cudaStream_t s) {
+    const int blocks = ((count + 1) / 2 + 255) / 256;
+    if (blocks <= 0) return cudaSuccess;
     if (record_bytes == 28)
-        packed_to_aos_kernel<float><<<blocks, 256, 0, s>>>(pos, vel_full, mass, n, (float*)aos, pos_lo_full, vel_lo_full);
+        packed_to_aos_kernel<float><<<blocks, 256, 0, s>>>(pos, vel, vel_first, mass, body_first, count, (float*)aos, pos_lo, vel_lo);
     else if (record_bytes == 56)
-        packed_to_aos_kernel<double><<<blocks, 256, 0, s>>>(pos, vel_full, mass, n, (double*)aos, pos_lo_full, vel_lo_full);
+        packed_to_aos_kernel<double><<<blocks, 256, 0, s>>>(pos, vel, vel_first, mass, body_first, count, (double*)aos, pos_lo, vel_lo);
     else
         return cudaErrorInvalidValue;
     return cudaGetLastError();

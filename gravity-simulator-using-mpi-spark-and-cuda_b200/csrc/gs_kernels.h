@@ -31,7 +31,7 @@ struct StepParams {
     float4* acc_out;         // kFinalAccOut: accelerations (x,y,z,0) per local body
     float4* partial;         // scratch [grid][2][i_tile]: partial sums of split i-tiles
     int n;                   // real bodies; bodies >= n are padding and are never moved
-    int i_begin;             // first body of this rank's slice (global index, multiple of kPadBodies)
+    int i_begin;             // first body of this rank's slice (global index, multiple of the i-tile)
     int ni_tiles;            // i-tiles in this rank's slice
     int nj_tiles;            // j-tiles covered by this launch (virtual index v in [0,nj_tiles))
     int nj_total;            // n_pad / kJTile
@@ -121,14 +121,22 @@ cudaError_t launch_sym_finish(const StepParams& p, const SymParams& sp, const in
 
 // AoS <-> packed-pair conversion on the device. `aos` is the raw byte image of the reference's
 // 28-byte (f32) or 56-byte (f64) records.  Bodies >= n are padding (mu = 0, at kPadPosition).
+// Covers bodies [body_first, body_first + body_count) (even bounds); the record of body i is record (i - rec_first).
+// Packed positions are stored into every buffer of `dst`: this GPU's two position buffers for a full upload, both
+// buffers of EVERY GPU (NVLink peer memory) when a rank uploads only its slice.
 // pos_lo_local / vel_lo_local (nullable): low-order words, i.e. what rounding the record to fp32 dropped.
-cudaError_t launch_aos_to_packed(const void* aos, int record_bytes, int n, int n_pad, double G,
-                                 float4* pos, float4* vel_local, double* mass, int i_begin,
-                                 int n_local_pad, float4* pos_lo_local, float4* vel_lo_local, cudaStream_t s);
-// pos_lo_full / vel_lo_full (nullable): added back in (exact for f64 records).
-cudaError_t launch_packed_to_aos(const float4* pos, const float4* vel_full, const double* mass,
-                                 int n, void* aos, int record_bytes, const float4* pos_lo_full,
-                                 const float4* vel_lo_full, cudaStream_t s);
+// mu_minmax: two words, preset to {0xffffffff, 0}: min and max bit pattern of mu over the real bodies.
+struct UploadTargets { int n; float4* pos[2 * (kMaxPeers + 1)]; };
+cudaError_t launch_aos_to_packed(const void* aos, int record_bytes, int rec_first, int n, int body_first,
+                                 int body_count, double G, const UploadTargets& dst, float4* vel_local, double* mass,
+                                 int i_begin, int n_local_pad, float4* pos_lo_local, float4* vel_lo_local,
+                                 uint32_t* mu_minmax, cudaStream_t s);
+cudaError_t launch_pack_minmax(uint32_t* mm4, cudaStream_t s);      // mm4[2] = mm4[0], mm4[3] = ~mm4[1]
+// Records of bodies [body_first, body_first + count) into aos[0..count): pos and mass are indexed globally, vel and
+// the (nullable) low-order words with (body - vel_first).
+cudaError_t launch_packed_to_aos(const float4* pos, const float4* vel, int vel_first, const double* mass,
+                                 int body_first, int count, void* aos, int record_bytes, const float4* pos_lo,
+                                 const float4* vel_lo, cudaStream_t s);
 
 // Energy diagnostics (fp64 accumulation).  potential: out_partials[gridDim] doubles, one per
 // CTA, of sum_i mu_i * sum_{j != i} mu_j / sqrt(r^2 + eps^2) over this rank's i-bodies (the caller

@@ -23,8 +23,6 @@ constexpr int kThreads = 256;     // threads per CTA of the force kernel
 constexpr int kJTile   = 512;     // bodies per j-tile = one TMA bulk copy of 8 KB
 constexpr int kStages  = 4;       // smem ring depth
 constexpr int kRefillLag = 2;     // a stage is refilled this many tiles after its use
-constexpr int kMaxITile = 2048;   // largest i-tile of any variant (scratch sizing)
-constexpr int kPadBodies = 2048;  // n_pad granularity per rank (multiple of every tile size)
 
 // Work unit u in [0, ni_tiles*nj_tiles): i-tile u / nj_tiles, (virtual) j-tile u % nj_tiles.
 // Persistent CTA c of `grid` owns the contiguous unit range [c*U/grid, (c+1)*U/grid).

@@ -3,6 +3,7 @@
 // libnccl.so.2 (e.g. torch's bundled copy) the dynamic loader hands back that same library.
 #pragma once
 #include <dlfcn.h>
+#include <mutex>
 #include <nccl.h>
 
 namespace gs {
@@ -19,17 +20,13 @@ struct NcclApi {
     bool ok = false;
 };
 
-inline NcclApi& nccl_api() {
-    static NcclApi api;
-    static bool tried = false;
-    if (tried) return api;
-    tried = true;
+inline void nccl_api_load(NcclApi& api) {
     const char* names[] = {"libnccl.so.2", "libnccl.so"};
     for (const char* nm : names) {
         api.handle = dlopen(nm, RTLD_NOW | RTLD_GLOBAL);
         if (api.handle) break;
     }
-    if (!api.handle) return api;
+    if (!api.handle) return;
 #define GS_SYM(field, name) *(void**)(&api.field) = dlsym(api.handle, name)
     GS_SYM(GetUniqueId, "ncclGetUniqueId");
     GS_SYM(CommInitRank, "ncclCommInitRank");
@@ -39,6 +36,13 @@ inline NcclApi& nccl_api() {
     GS_SYM(GetErrorString, "ncclGetErrorString");
 #undef GS_SYM
     api.ok = api.GetUniqueId && api.CommInitRank && api.CommDestroy && api.AllGather && api.AllReduce;
+}
+
+// Loaded once, whichever rank thread gets here first (one thread per GPU in the CLI and the tests).
+inline NcclApi& nccl_api() {
+    static NcclApi api;
+    static std::once_flag once;
+    std::call_once(once, [] { nccl_api_load(api); });
     return api;
 }
 

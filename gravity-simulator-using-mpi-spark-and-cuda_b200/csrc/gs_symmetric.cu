@@ -43,12 +43,18 @@ constexpr size_t sym_smem_for(int threads) {
 //               distinct bodies within 1e-10 of each other, i.e. (in fp32) coincident bodies.
 enum SymCut : int { kSymSoft = 0, kSymSelect = 1, kSymTrack = 2 };
 
-// One j-tile, both directions.  accA/accB: THIS warp's j-side running sums ({ax0,ax1,ay0,ay1}, {az0,az1} per j-pair).
-// NPAIR j-pairs per lane and iteration (pairs q, q+32, ... of a 32*NPAIR-pair chunk, q = (it + lane) mod 32):
-// more independent chains between two __syncwarp()s.
+// One j-tile, both directions.  NPAIR j-pairs per lane and iteration (pairs q, q+32, ... of a 32*NPAIR-pair chunk,
+// q = (it + lane) mod 32): NPAIR * R independent chains per iteration.
+// How a j-pair's running sums follow the pair from lane to lane (it is worked on by lane l in iteration `it` and by
+// lane l-1 in iteration it+1):
+//   SHFL = true : they stay in registers and move with six 32-bit shuffles per pair and iteration; after the 32
+//                 iterations of a chunk every pair has been round the warp once and its sums are stored, once, into
+//                 this warp's accA/accB ({ax0,ax1,ay0,ay1}, {az0,az1} per j-pair; plain stores, nothing to clear);
+//   SHFL = false: read-modify-write of accA/accB every iteration with a __syncwarp() in between (the first version
+//                 of this pass; kept for A/B measurements: the round trip through shared memory costs ~9 %).
 // Returns true (warp-uniform, kSymTrack only) when the unit has to be redone with the select; `out` is then untouched
 // and the warp's accA/accB hold garbage.
-template <int R, int CUT, bool UNI, int NPAIR, int PROBE = 0>
+template <int R, int CUT, bool UNI, int NPAIR, bool SHFL>
 __device__ __forceinline__ bool sym_tile(const float4* __restrict__ T, float4* __restrict__ accA,
                                          float2* __restrict__ accB, int lane, const float2 (&nxi)[R],
                                          const float2 (&nyi)[R], const float2 (&nzi)[R], const float2 (&nmui)[R],
@@ -59,70 +65,90 @@ __device__ __forceinline__ bool sym_tile(const float4* __restrict__ T, float4* _
     for (int b = 0; b < R; ++b) ax[b] = ay[b] = az[b] = make_float2(0.f, 0.f);
 #pragma unroll
     for (int h = 0; h < NPAIR; ++h) rmin[h] = 3.0e38f;
-    // PROBE (timing experiments only, results are wrong): 1 = j-side sums never leave the registers (no LDS/STS
-    // round trip, no __syncwarp), 2 = j-tile read as if A and B records were de-interleaved (conflict-free), 3 = both
-    float4 PJA[NPAIR]; float2 PJB[NPAIR];
-    if (PROBE & 1) {
+    const int from = (lane + 1) & 31;       // the lane that worked on "my next pair" in this iteration
+    // one j-pair (records A, B) against the R i-bodies, both directions
+    auto pair_step = [&](const float4& A, const float4& B, float2& jx, float2& jy, float2& jz, float& rm) {
+        const float2 xj = make_float2(A.x, A.y), yj = make_float2(A.z, A.w);
+        const float2 zj = make_float2(B.x, B.y), mj = make_float2(B.z, B.w);
 #pragma unroll
-        for (int h = 0; h < NPAIR; ++h) { PJA[h] = make_float4(0.f, 0.f, 0.f, 0.f); PJB[h] = make_float2(0.f, 0.f); }
-    }
-    for (int chunk = 0; chunk < kJTile / (64 * NPAIR); ++chunk) {
-#pragma unroll 1
-        for (int it = 0; it < 32; ++it) {
-            const int p0 = chunk * (32 * NPAIR) + ((it + lane) & 31);
-            float4 JA[NPAIR], A[NPAIR], B[NPAIR];
-            float2 JB[NPAIR];
-#pragma unroll
-            for (int h = 0; h < NPAIR; ++h) {
-                if (PROBE & 2) { A[h] = T[p0 + 32 * h]; B[h] = T[kJTile / 2 + p0 + 32 * h]; }
-                else { A[h] = T[2 * (p0 + 32 * h)]; B[h] = T[2 * (p0 + 32 * h) + 1]; }
-                if (PROBE & 1) { JA[h] = PJA[h]; JB[h] = PJB[h]; }
-                else { JA[h] = accA[p0 + 32 * h]; JB[h] = accB[p0 + 32 * h]; }
+        for (int b = 0; b < R; ++b) {
+            const float2 dx = __fadd2_rn(xj, nxi[b]);
+            const float2 dy = __fadd2_rn(yj, nyi[b]);
+            const float2 dz = __fadd2_rn(zj, nzi[b]);
+            float2 r2 = __ffma2_rn(dx, dx, eps2);
+            r2 = __ffma2_rn(dy, dy, r2);
+            r2 = __ffma2_rn(dz, dz, r2);
+            float2 ri = make_float2(rsqrt_approx(r2.x), rsqrt_approx(r2.y));
+            if (CUT == kSymSelect) {
+                ri.x = (r2.x >= cut2) ? ri.x : 0.f;
+                ri.y = (r2.y >= cut2) ? ri.y : 0.f;
             }
-#pragma unroll
-            for (int h = 0; h < NPAIR; ++h) {
-                const float2 xj = make_float2(A[h].x, A[h].y), yj = make_float2(A[h].z, A[h].w);
-                const float2 zj = make_float2(B[h].x, B[h].y), mj = make_float2(B[h].z, B[h].w);
-                float2 jx = make_float2(JA[h].x, JA[h].y), jy = make_float2(JA[h].z, JA[h].w), jz = JB[h];
-#pragma unroll
-                for (int b = 0; b < R; ++b) {
-                    const float2 dx = __fadd2_rn(xj, nxi[b]);
-                    const float2 dy = __fadd2_rn(yj, nyi[b]);
-                    const float2 dz = __fadd2_rn(zj, nzi[b]);
-                    float2 r2 = __ffma2_rn(dx, dx, eps2);
-                    r2 = __ffma2_rn(dy, dy, r2);
-                    r2 = __ffma2_rn(dz, dz, r2);
-                    float2 ri = make_float2(rsqrt_approx(r2.x), rsqrt_approx(r2.y));
-                    if (CUT == kSymSelect) {
-                        ri.x = (r2.x >= cut2) ? ri.x : 0.f;
-                        ri.y = (r2.y >= cut2) ? ri.y : 0.f;
-                    }
-                    if (CUT == kSymTrack) asm("min.f32 %0, %0, %1, %2;" : "+f"(rmin[h]) : "f"(r2.x), "f"(r2.y));   // FMNMX3
-                    const float2 ri2 = __fmul2_rn(ri, ri);
-                    const float2 t = __fmul2_rn(ri2, ri);                       // rinv^3, shared by both directions
-                    const float2 s = UNI ? t : __fmul2_rn(mj, t);               // on i:  +mu_j t d
-                    const float2 u = UNI ? t : __fmul2_rn(nmui[b], t);          // on j:  -mu_i t d  (UNI: sign and mu at the flush)
-                    ax[b] = __ffma2_rn(s, dx, ax[b]);
-                    ay[b] = __ffma2_rn(s, dy, ay[b]);
-                    az[b] = __ffma2_rn(s, dz, az[b]);
-                    jx = __ffma2_rn(u, dx, jx);
-                    jy = __ffma2_rn(u, dy, jy);
-                    jz = __ffma2_rn(u, dz, jz);
-                }
-                JA[h] = make_float4(jx.x, jx.y, jy.x, jy.y);
-                JB[h] = jz;
-            }
-#pragma unroll
-            for (int h = 0; h < NPAIR; ++h) {
-                if (PROBE & 1) { PJA[h] = JA[h]; PJB[h] = JB[h]; }
-                else { accA[p0 + 32 * h] = JA[h]; accB[p0 + 32 * h] = JB[h]; }
-            }
-            if (!(PROBE & 1)) __syncwarp();     // next iteration another lane picks these pairs up
+            if (CUT == kSymTrack) asm("min.f32 %0, %0, %1, %2;" : "+f"(rm) : "f"(r2.x), "f"(r2.y));   // FMNMX3
+            const float2 ri2 = __fmul2_rn(ri, ri);
+            const float2 t = __fmul2_rn(ri2, ri);                       // rinv^3, shared by both directions
+            const float2 s = UNI ? t : __fmul2_rn(mj, t);               // on i:  +mu_j t d
+            const float2 u = UNI ? t : __fmul2_rn(nmui[b], t);          // on j:  -mu_i t d  (UNI: sign and mu at the flush)
+            ax[b] = __ffma2_rn(s, dx, ax[b]);
+            ay[b] = __ffma2_rn(s, dy, ay[b]);
+            az[b] = __ffma2_rn(s, dz, az[b]);
+            jx = __ffma2_rn(u, dx, jx);
+            jy = __ffma2_rn(u, dy, jy);
+            jz = __ffma2_rn(u, dz, jz);
         }
-    }
-    if (PROBE & 1) {
+    };
+    constexpr int NCHUNK = kJTile / (64 * NPAIR);
+    if (SHFL) {
+        for (int chunk = 0; chunk < NCHUNK; ++chunk) {
+            float2 jx[NPAIR], jy[NPAIR], jz[NPAIR];
 #pragma unroll
-        for (int h = 0; h < NPAIR; ++h) { accA[lane + 32 * h] = PJA[h]; accB[lane + 32 * h] = PJB[h]; }
+            for (int h = 0; h < NPAIR; ++h) jx[h] = jy[h] = jz[h] = make_float2(0.f, 0.f);
+#pragma unroll 1
+            for (int it = 0; it < 32; ++it) {
+                const int p0 = chunk * (32 * NPAIR) + ((it + lane) & 31);
+                float4 A[NPAIR], B[NPAIR];
+#pragma unroll
+                for (int h = 0; h < NPAIR; ++h) { A[h] = T[2 * (p0 + 32 * h)]; B[h] = T[2 * (p0 + 32 * h) + 1]; }
+#pragma unroll
+                for (int h = 0; h < NPAIR; ++h) pair_step(A[h], B[h], jx[h], jy[h], jz[h], rmin[h]);
+                // (measured: issuing each group's shuffles right after the group, with the next iteration's first
+                // loads prefetched, is 2.5 % slower -- ptxas sinks them to the end anyway and the loop gets longer)
+#pragma unroll
+                for (int h = 0; h < NPAIR; ++h) {
+                    jx[h].x = __shfl_sync(0xffffffffu, jx[h].x, from); jx[h].y = __shfl_sync(0xffffffffu, jx[h].y, from);
+                    jy[h].x = __shfl_sync(0xffffffffu, jy[h].x, from); jy[h].y = __shfl_sync(0xffffffffu, jy[h].y, from);
+                    jz[h].x = __shfl_sync(0xffffffffu, jz[h].x, from); jz[h].y = __shfl_sync(0xffffffffu, jz[h].y, from);
+                }
+            }
+            // after 32 shuffles lane l holds the finished sums of pair l (+ 32h) of this chunk
+#pragma unroll
+            for (int h = 0; h < NPAIR; ++h) {
+                accA[chunk * (32 * NPAIR) + lane + 32 * h] = make_float4(jx[h].x, jx[h].y, jy[h].x, jy[h].y);
+                accB[chunk * (32 * NPAIR) + lane + 32 * h] = jz[h];
+            }
+        }
+    } else {
+        for (int chunk = 0; chunk < NCHUNK; ++chunk) {
+#pragma unroll 1
+            for (int it = 0; it < 32; ++it) {
+                const int p0 = chunk * (32 * NPAIR) + ((it + lane) & 31);
+                float4 A[NPAIR], B[NPAIR];
+                float2 jx[NPAIR], jy[NPAIR], jz[NPAIR];
+#pragma unroll
+                for (int h = 0; h < NPAIR; ++h) {
+                    A[h] = T[2 * (p0 + 32 * h)]; B[h] = T[2 * (p0 + 32 * h) + 1];
+                    const float4 JA = accA[p0 + 32 * h];
+                    jx[h] = make_float2(JA.x, JA.y); jy[h] = make_float2(JA.z, JA.w); jz[h] = accB[p0 + 32 * h];
+                }
+#pragma unroll
+                for (int h = 0; h < NPAIR; ++h) pair_step(A[h], B[h], jx[h], jy[h], jz[h], rmin[h]);
+#pragma unroll
+                for (int h = 0; h < NPAIR; ++h) {
+                    accA[p0 + 32 * h] = make_float4(jx[h].x, jx[h].y, jy[h].x, jy[h].y);
+                    accB[p0 + 32 * h] = jz[h];
+                }
+                __syncwarp();     // next iteration another lane picks these pairs up
+            }
+        }
     }
     if (CUT == kSymTrack) {
         float m = rmin[0];
@@ -139,7 +165,7 @@ __device__ __forceinline__ bool sym_tile(const float4* __restrict__ T, float4* _
     return false;
 }
 
-template <int R, int THREADS, int CUT, bool UNI, int NPAIR, int PROBE = 0>
+template <int R, int THREADS, int CUT, bool UNI, int NPAIR, bool SHFL>
 __global__ void __launch_bounds__(THREADS, 1) sym_force_kernel(const SymParams p) {
     constexpr int ITILE = THREADS * R;
     constexpr int NP = R / 2;
@@ -166,10 +192,11 @@ __global__ void __launch_bounds__(THREADS, 1) sym_force_kernel(const SymParams p
         }
         fence_mbar_init();
     }
-    for (int e = lane; e < kJTile / 2; e += 32) {
-        accA[e] = make_float4(0.f, 0.f, 0.f, 0.f);
-        accB[e] = make_float2(0.f, 0.f);
-    }
+    if (!SHFL)
+        for (int e = lane; e < kJTile / 2; e += 32) {
+            accA[e] = make_float4(0.f, 0.f, 0.f, 0.f);
+            accB[e] = make_float2(0.f, 0.f);
+        }
     __syncthreads();
 
     // producer cursor: the next unit whose j-tile has to be loaded (only thread 0 uses it)
@@ -218,15 +245,17 @@ __global__ void __launch_bounds__(THREADS, 1) sym_force_kernel(const SymParams p
             if (!symmetric) {
                 // the row's own j-tiles hold the i-bodies themselves: one direction, select on every interaction
                 tile_packed<R, (CUT == kSymSoft ? kSoftened : kCutoff), UNI, 2>(T, nxi, nyi, nzi, eps2, p.cut2, acc);
-            } else if (sym_tile<R, CUT, UNI, NPAIR, PROBE>(T, accA, accB, lane, nxi, nyi, nzi, nmui, eps2, p.cut2, acc)) {
+            } else if (sym_tile<R, CUT, UNI, NPAIR, SHFL>(T, accA, accB, lane, nxi, nyi, nzi, nmui, eps2, p.cut2, acc)) {
                 // kSymTrack only: something of this warp came within the cutoff (coincident bodies) -- exact redo
-                for (int e = lane; e < kJTile / 2; e += 32) {
-                    accA[e] = make_float4(0.f, 0.f, 0.f, 0.f);
-                    accB[e] = make_float2(0.f, 0.f);
+                if (!SHFL) {
+                    for (int e = lane; e < kJTile / 2; e += 32) {
+                        accA[e] = make_float4(0.f, 0.f, 0.f, 0.f);
+                        accB[e] = make_float2(0.f, 0.f);
+                    }
+                    __syncwarp();
                 }
-                __syncwarp();
-                sym_tile<R, kSymSelect, UNI, (CUT == kSymTrack ? 2 : NPAIR)>(T, accA, accB, lane, nxi, nyi, nzi, nmui, eps2,
-                                                                           p.cut2, acc);
+                sym_tile<R, kSymSelect, UNI, (CUT == kSymTrack ? 2 : NPAIR), SHFL>(T, accA, accB, lane, nxi, nyi, nzi, nmui,
+                                                                                 eps2, p.cut2, acc);
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty[stage]);
@@ -245,14 +274,22 @@ __global__ void __launch_bounds__(THREADS, 1) sym_force_kernel(const SymParams p
                         const float4 a = accA_all[wv * (kJTile / 2) + e];
                         const float2 b = accB_all[wv * (kJTile / 2) + e];
                         SA.x += a.x; SA.y += a.y; SA.z += a.z; SA.w += a.w; SB.x += b.x; SB.y += b.y;
-                        accA_all[wv * (kJTile / 2) + e] = make_float4(0.f, 0.f, 0.f, 0.f);
-                        accB_all[wv * (kJTile / 2) + e] = make_float2(0.f, 0.f);
+                        if (!SHFL) {
+                            accA_all[wv * (kJTile / 2) + e] = make_float4(0.f, 0.f, 0.f, 0.f);
+                            accB_all[wv * (kJTile / 2) + e] = make_float2(0.f, 0.f);
+                        }
                     }
                     // System scope: the owner's SMs and every peer's add into the same words, over NVLink for a
                     // remote owner; only system-scope atomics are guaranteed atomic across GPUs (SASS: RED...SYS).
+                    // On one GPU device scope is enough.
                     float* dst = jbase + 4 * (2 * e);                          // bodies 2e, 2e+1 of the tile
-                    atomicAdd_system(dst + 0, w * SA.x); atomicAdd_system(dst + 1, w * SA.z); atomicAdd_system(dst + 2, w * SB.x);
-                    atomicAdd_system(dst + 4, w * SA.y); atomicAdd_system(dst + 5, w * SA.w); atomicAdd_system(dst + 6, w * SB.y);
+                    if (p.world > 1) {
+                        atomicAdd_system(dst + 0, w * SA.x); atomicAdd_system(dst + 1, w * SA.z); atomicAdd_system(dst + 2, w * SB.x);
+                        atomicAdd_system(dst + 4, w * SA.y); atomicAdd_system(dst + 5, w * SA.w); atomicAdd_system(dst + 6, w * SB.y);
+                    } else {
+                        atomicAdd(dst + 0, w * SA.x); atomicAdd(dst + 1, w * SA.z); atomicAdd(dst + 2, w * SB.x);
+                        atomicAdd(dst + 4, w * SA.y); atomicAdd(dst + 5, w * SA.w); atomicAdd(dst + 6, w * SB.y);
+                    }
                 }
                 __syncthreads();
             }
@@ -346,39 +383,35 @@ void build_sym_plan(const SymParams& sp, int grid, int cost_plain, int cost_sym,
 }
 
 typedef void (*SymKernel)(const SymParams);
-static int sym_npair() {       // j-pairs per lane and iteration (GRAVSIM_SYM_NPAIR: measurement knob)
-    static int v = 0;
-    if (!v) { const char* e = getenv("GRAVSIM_SYM_NPAIR"); v = (e && atoi(e) == 2) ? 2 : (e && atoi(e) == 4) ? 4 : kSymDefaultNPair; }
-    return v;
-}
+static int env_int(const char* name, int dflt) { const char* e = getenv(name); return e ? atoi(e) : dflt; }
+// measurement knobs: j-pairs per lane and iteration; 0 = j-side sums through shared memory (old scheme)
+// (read at every launch, not cached: the probes switch them inside one process)
+static int sym_npair() { const int v = env_int("GRAVSIM_SYM_NPAIR", 0); return (v == 2 || v == 4) ? v : kSymDefaultNPair; }
+static bool sym_shfl() { return env_int("GRAVSIM_SYM_SHFL", 1) != 0; }
 static int sym_cut_of(int cut_mode) {
     return cut_mode == kSoftened ? kSymSoft : cut_mode == kCutoff ? kSymSelect : kSymTrack;
 }
-template <int RR, int TH, int NP>
+template <int RR, int TH, int NP, bool SH>
 static SymKernel pick_sym_rn(int cut, bool uni) {
     switch (sym_cut_of(cut)) {
-        case kSymSoft: return uni ? (SymKernel)sym_force_kernel<RR, TH, kSymSoft, true, NP> : (SymKernel)sym_force_kernel<RR, TH, kSymSoft, false, NP>;
-        case kSymSelect: return uni ? (SymKernel)sym_force_kernel<RR, TH, kSymSelect, true, NP> : (SymKernel)sym_force_kernel<RR, TH, kSymSelect, false, NP>;
-        default: return uni ? (SymKernel)sym_force_kernel<RR, TH, kSymTrack, true, NP> : (SymKernel)sym_force_kernel<RR, TH, kSymTrack, false, NP>;
+        case kSymSoft: return uni ? (SymKernel)sym_force_kernel<RR, TH, kSymSoft, true, NP, SH> : (SymKernel)sym_force_kernel<RR, TH, kSymSoft, false, NP, SH>;
+        case kSymSelect: return uni ? (SymKernel)sym_force_kernel<RR, TH, kSymSelect, true, NP, SH> : (SymKernel)sym_force_kernel<RR, TH, kSymSelect, false, NP, SH>;
+        default: return uni ? (SymKernel)sym_force_kernel<RR, TH, kSymTrack, true, NP, SH> : (SymKernel)sym_force_kernel<RR, TH, kSymTrack, false, NP, SH>;
     }
+}
+template <int RR, int TH>
+static SymKernel pick_sym_t(int cut, bool uni) {
+    const int np = sym_npair();
+    if (sym_shfl()) return np == 4 ? pick_sym_rn<RR, TH, 4, true>(cut, uni) : pick_sym_rn<RR, TH, 2, true>(cut, uni);
+    return np == 4 ? pick_sym_rn<RR, TH, 4, false>(cut, uni) : pick_sym_rn<RR, TH, 2, false>(cut, uni);
 }
 // (i-bodies per thread, threads per CTA) pairs the pass is built for
 static SymKernel pick_sym(int R, int threads, int cut, bool uni) {
-    const int np = sym_npair();
-    if (const char* pe = getenv("GRAVSIM_SYM_PROBE")) {     // timing experiments (wrong results), headline configuration only
-        if (R == 8 && threads == 256 && cut == kSoftened && uni) {
-            if (atoi(pe) == 1) return (SymKernel)sym_force_kernel<8, 256, kSymSoft, true, 4, 1>;
-            if (atoi(pe) == 2) return (SymKernel)sym_force_kernel<8, 256, kSymSoft, true, 4, 2>;
-            if (atoi(pe) == 3) return (SymKernel)sym_force_kernel<8, 256, kSymSoft, true, 4, 3>;
-        }
-    }
-    if (threads == 256) {
-        if (R == 4) return np == 4 ? pick_sym_rn<4, 256, 4>(cut, uni) : pick_sym_rn<4, 256, 2>(cut, uni);
-        if (R == 6) return np == 4 ? pick_sym_rn<6, 256, 4>(cut, uni) : pick_sym_rn<6, 256, 2>(cut, uni);
-        if (R == 8) return np == 4 ? pick_sym_rn<8, 256, 4>(cut, uni) : pick_sym_rn<8, 256, 2>(cut, uni);
-    }
-    if (threads == 384 && R == 8) return pick_sym_rn<8, 384, 2>(cut, uni);
-    if (threads == 512 && R == 4) return np == 4 ? pick_sym_rn<4, 512, 4>(cut, uni) : pick_sym_rn<4, 512, 2>(cut, uni);
+    if (threads == 256 && R == 4) return pick_sym_t<4, 256>(cut, uni);
+    if (threads == 256 && R == 6) return pick_sym_t<6, 256>(cut, uni);
+    if (threads == 256 && R == 8) return pick_sym_t<8, 256>(cut, uni);
+    if (threads == 384 && R == 8) return sym_shfl() ? pick_sym_rn<8, 384, 2, true>(cut, uni) : pick_sym_rn<8, 384, 2, false>(cut, uni);
+    if (threads == 512 && R == 4) return pick_sym_t<4, 512>(cut, uni);
     return nullptr;
 }
 

@@ -119,6 +119,17 @@ int gs_upload_aos_f64(gs_ctx *ctx, const void *particles56, int n);
 int gs_download_aos_f32(gs_ctx *ctx, void *particles28, int n);
 int gs_download_aos_f64(gs_ctx *ctx, void *particles56, int n);
 
+/* The same for ONE rank's own records: rank r passes / receives exactly the records of its i-bodies,
+ * first = gs_info.i_begin, count = gs_info.i_end - gs_info.i_begin (else GS_EINVAL) -- the slice mpi.c:184-187
+ * assigns to it and mpi.c:196-216 updates.  Collective like the full-array calls when world_size > 1, but each GPU
+ * moves n/world_size records over PCIe; the packed positions reach the other GPUs by NVLink stores (this replaces the
+ * MPI_Bcast of mpi.c:182 by "every rank contributes its part", as MPI_Allgatherv does at mpi.c:227-231).  A download
+ * of a slice touches no other GPU. */
+int gs_upload_slice_f32(gs_ctx *ctx, const void *my_particles28, int first, int count);
+int gs_upload_slice_f64(gs_ctx *ctx, const void *my_particles56, int first, int count);
+int gs_download_slice_f32(gs_ctx *ctx, void *my_particles28, int first, int count);
+int gs_download_slice_f64(gs_ctx *ctx, void *my_particles56, int first, int count);
+
 /* ---- the hot path ------------------------------------------------------------------------ */
 
 /* Replaces the step loops cuda.cu:155-163 (kernel, sync, D2H, host update) and mpi.c:191-237

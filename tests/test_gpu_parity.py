@@ -336,6 +336,38 @@ def test_trajectory_recording(gs):
 
 
 # ---- boundary behaviour -------------------------------------------------------------------------------
+def test_slice_upload_download_one_gpu(gs, oracle):
+    # with one rank the slice is the whole array; also the device-side equal-mass detection
+    n = 5001
+    b = gs.ic_reference_uniform(n, seed=21)
+    with gs.GravSim(n) as sim:
+        assert sim.my_range == (0, n)
+        sim.upload_slice(b)
+        assert sim.info.uniform_mass == 0
+        assert np.array_equal(sim.download(), b) and np.array_equal(sim.download_slice(), b)
+        sim.step(3)
+        out = sim.download_slice(np.float64)
+        assert np.array_equal(out, sim.download(np.float64))
+        with pytest.raises(gs.GravSimError):
+            sim.upload_slice(b[:100])                                   # not this rank's slice: GS_EINVAL
+    ref = oracle.run_sync(b.astype(np.float64), 3600.0, 3)
+    assert np.abs(out[:, :3] - ref[:, :3]).max() <= 2e-6 * 3e11
+    p = gs.ic_plummer(n, seed=3)
+    with gs.GravSim(n, G=1.0, eps=0.01) as sim:
+        sim.upload(p)
+        assert sim.info.uniform_mass == 1
+        p2 = p.copy(); p2[n - 1, 6] *= 2.0
+        sim.upload(p2)
+        assert sim.info.uniform_mass == 0
+        p2[n - 1, 6] = 0.0                                              # massless last body: not "all equal" either
+        sim.upload_slice(p2)
+        assert sim.info.uniform_mass == 0
+    with gs.GravSim(n, G=1.0, eps=0.01, flags=gs.FLAG_NO_UNIFORM_MASS) as sim:
+        sim.upload(p)
+        assert sim.info.uniform_mass == 0
+
+
+
 def test_round_trip_accel_is_pure_and_deterministic(gs):
     b = gs.ic_reference_uniform(2500, seed=9)
     with gs.GravSim(2500, flags=DET) as sim:
@@ -461,7 +493,10 @@ def test_multi_gpu_symmetric_pass(gs, oracle, W):
     ref = oracle.accel_subset(b.astype(np.float64), np.arange(n), massfree=True)[0]
     assert np.isfinite(a).all() and rel_err(a, ref).max() <= ACC_TOL
     # (3) default variant choice at this N and W, several steps, trajectory against the synchronous oracle
+    # (without the two bodies 5 m from the Sun: their 1e18 m/s^2 would swamp an absolute position bound)
     steps = 2
+    u = gs.ic_reference_uniform(n, seed=50 + W)
+    u[n - 7] = u[11]
 
     def work(rank, uid):
         with gs.GravSim(n, device=rank, rank=rank, world_size=W, nccl_id=uid) as sim:
@@ -473,6 +508,27 @@ def test_multi_gpu_symmetric_pass(gs, oracle, W):
     for rank in range(W):
         assert np.abs(res[rank][:, :3] - ref[:, :3]).max() <= 2e-6 * 3e11
         assert np.array_equal(res[rank], res[0])
+    # (4) every rank uploads and downloads only the records of its own bodies (mpi.c:184-187's slice); positions
+    # reach the peers by NVLink stores, equal masses are detected across ranks on the device
+    pl = gs.ic_plummer(n, seed=60 + W)
+
+    def work_slices(rank, uid):
+        with gs.GravSim(n, device=rank, rank=rank, world_size=W, nccl_id=uid, variant=3) as sim:
+            lo, hi = sim.my_range
+            sim.upload_slice(pl[lo:hi])
+            uni = sim.info.uniform_mass
+            sim.upload_slice(u[lo:hi])                       # a second upload over a used context
+            assert sim.info.uniform_mass == 0
+            sim.step(steps)
+            part = sim.download_slice()
+            return lo, hi, uni, part, sim.download()
+    res = _run_ranks(gs, W, work_slices)
+    assert sum(r[1] - r[0] for r in res) == n
+    for lo, hi, uni, part, full in res:
+        assert uni == 1
+        assert np.array_equal(full[lo:hi], part) and np.array_equal(full, res[0][4])
+        assert np.array_equal(full[:, 6], u[:, 6])           # masses come back exactly, from every rank
+        assert np.abs(full[:, :3] - ref[:, :3]).max() <= 2e-6 * 3e11
 
 
 def test_multi_gpu_symmetric_pass_1M_all_gpus(gs, oracle):

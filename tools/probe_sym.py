@@ -9,10 +9,11 @@ from __graft_entry__ import load_package  # noqa: E402
 
 gs = load_package()
 PEAK = 148 * 128 * 2 * 1.965e9
-KNOBS = ("GRAVSIM_SYM_NPAIR", "GRAVSIM_SYM_PROBE", "GRAVSIM_CUTMODE", "GRAVSIM_GRID", "GRAVSIM_SYM_COST")
+KNOBS = ("GRAVSIM_SYM_NPAIR", "GRAVSIM_SYM_SHFL", "GRAVSIM_SYM_PROBE", "GRAVSIM_CUTMODE", "GRAVSIM_GRID", "GRAVSIM_SYM_COST")
 
 
-def probe(n, variant, eps, flags, env, steps=4):
+def probe(n, variant, eps, flags, env, steps=None):
+    steps = steps or max(4, int(2e12 / (float(n) * n)))
     for k in KNOBS:
         os.environ.pop(k, None)
     os.environ.update(env)
