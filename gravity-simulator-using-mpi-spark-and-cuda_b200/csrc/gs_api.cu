@@ -80,8 +80,8 @@ struct gs_ctx {
     int sym_grid = 0, sym_regs = 0, sym_cut_mode = 0;
     SymCta* d_sym_ctas = nullptr;
     int2* d_sym_rows = nullptr;
-    float* d_accj = nullptr;                    // j-side sums of MY bodies (peers add into it over NVLink)
-    float* peer_accj[kMaxPeers + 1] = {};       // every rank's accj as seen from this GPU
+    long long* d_accj = nullptr;                // j-side sums of MY bodies, wide fixed point (peers add into it over NVLink)
+    long long* peer_accj[kMaxPeers + 1] = {};   // every rank's accj as seen from this GPU
     float4* sym_partial = nullptr;
     bool want_sym = false, p2p_atomics = false;
     uint32_t fstep = 0;                         // symmetric passes whose remote atomics were fenced so far
@@ -377,7 +377,7 @@ int setup_peer_exchange(gs_ctx* c) {
             }
             c->peer_pos[0][q] = (float4*)mapped[0]; c->peer_pos[1][q] = (float4*)mapped[1];
             c->peer_flags[q] = (uint32_t*)mapped[2];
-            c->peer_accj[q] = (float*)mapped[3];
+            c->peer_accj[q] = (long long*)mapped[3];
         }
         if (ok) ok = atomics ? 2 : 1;      // min over ranks: 0 no peer access, 1 stores only, 2 stores + atomics
         // unanimous decision
@@ -743,8 +743,9 @@ int gs_create(gs_ctx** out, const gs_config* cfg) {
     c->want_sym = !(c->cfg.flags & GS_FLAG_DETERMINISTIC) && sym_supported(c->R, c->threads) &&
                   cfg->world_size <= kMaxPeers + 1;
     if (c->want_sym) {      // allocated now so that setup_peer_exchange() can publish it to the peers
-        if (!dmalloc((void**)&c->d_accj, vel_bytes)) return fail(GS_ENOMEM);
-        if (cudaMemset(c->d_accj, 0, vel_bytes) != cudaSuccess) return fail(GS_ECUDA);
+        const size_t accj_bytes = (size_t)c->slice * kSymAccjBytesPerBody;
+        if (!dmalloc((void**)&c->d_accj, accj_bytes)) return fail(GS_ENOMEM);
+        if (cudaMemset(c->d_accj, 0, accj_bytes) != cudaSuccess) return fail(GS_ECUDA);
         c->peer_accj[cfg->rank] = c->d_accj;
     }
     if ((cfg->world_size > 1 || (c->cfg.flags & GS_FLAG_TWO_PASS)) && !dmalloc((void**)&c->acc_local, vel_bytes))

@@ -51,6 +51,56 @@ __device__ __forceinline__ float rsqrt_approx(float x) {
 }
 
 // ------------------------------------------------------------------------------------------------
+// Order-independent sums of floats: wide fixed point.
+// The j-side sums of the pair-symmetric pass are added up by many CTAs (and GPUs) in an order that depends on
+// timing.  Floating-point atomics would make the last bits of every run different; integer addition is
+// associative, so each float is added EXACTLY into a 160-bit fixed-point number (kFxLimbs 64-bit words holding
+// base-2^32 digits, least significant bit 2^kFxLsb) with two integer atomics.  The result does not depend on the
+// order of the additions: the default pass is bit-reproducible.
+// Window: magnitudes in [2^-80, 2^71) (8e-25 .. 2.4e21 in whatever units the accelerations have); smaller
+// contributions are truncated towards -inf bit by bit, larger ones saturate -- both deterministically.
+// ------------------------------------------------------------------------------------------------
+constexpr int kFxLimbs = 5;
+constexpr int kFxLsb = -80;
+constexpr int kFxWordsPerBody = 3 * kFxLimbs;     // x, y, z
+
+// limbs[k * stride] is limb k
+template <bool SYS>
+__device__ __forceinline__ void fx_add(long long* limbs, int stride, float v) {
+    const int bits = __float_as_int(v);
+    const int e = (bits >> 23) & 0xff;
+    if (e == 0) return;                                     // zero (denormals count as zero)
+    long long m = (long long)((bits & 0x7fffff) | 0x800000);
+    int s = e - 150 - kFxLsb;                               // v = +-m * 2^(e - 150) = +-m * 2^s * 2^kFxLsb
+    if (e == 0xff || s > 32 * (kFxLimbs - 2) + 31) { s = 32 * (kFxLimbs - 2) + 31; m = 0xffffff; }   // inf/NaN/huge: saturate
+    if (bits < 0) m = -m;
+    if (s < 0) {
+        if (s < -24) return;
+        m >>= -s;                                           // arithmetic shift: floor
+        s = 0;
+    }
+    const int k = s >> 5;
+    const long long X = m << (s & 31);                      // |X| < 2^55
+    const unsigned long long lo = (unsigned long long)(X & 0xffffffffll);
+    const long long hi = X >> 32;                           // X = hi * 2^32 + lo exactly
+    unsigned long long* w = reinterpret_cast<unsigned long long*>(limbs) + (size_t)k * stride;
+    if (SYS) {
+        if (lo) atomicAdd_system(w, lo);
+        if (hi) atomicAdd_system(w + stride, (unsigned long long)hi);
+    } else {
+        if (lo) atomicAdd(w, lo);
+        if (hi) atomicAdd(w + stride, (unsigned long long)hi);
+    }
+}
+// The accumulated value, rounded once; reads the limbs in a fixed order (deterministic).
+__device__ __forceinline__ float fx_value(const long long* limbs) {
+    double v = 0.0;
+#pragma unroll
+    for (int k = kFxLimbs - 1; k >= 0; --k) v += ldexp((double)limbs[k], 32 * k + kFxLsb);
+    return (float)v;
+}
+
+// ------------------------------------------------------------------------------------------------
 // finishing one i-pair: add upstream accelerations, then write them out or integrate
 //   v += a * kick_dt ; x += v_new * drift_dt          (cuda.cu:73-76, mpi.c:207-215)
 // ------------------------------------------------------------------------------------------------

@@ -21,6 +21,7 @@ constexpr float kPadPosition = 1.0e18f;   // padding bodies: (1e18,1e18,1e18), m
 struct VariantInfo { int R, threads, unroll, packed, i_tile; };
 bool variant_info(int variant, VariantInfo* out);     // false if the variant does not exist
 
+constexpr int kSymAccjBytesPerBody = 3 * 5 * 8;   // = kFxWordsPerBody * sizeof(long long), checked in gs_symmetric.cu
 constexpr int kMaxPeers = 7;   // direct peer-memory exchange supports up to 8 GPUs (one NVSwitch domain)
 
 struct StepParams {
@@ -77,8 +78,10 @@ struct SymParams {
     const float4* pos;       // packed pairs, n_pad bodies (every rank's)
     float4* acc_whole;       // i-side sums of rows handled by a single CTA (float4 per local body)
     float4* partial;         // [grid][2][i_tile]: i-side sums of rows split between CTAs
-    float* accj[kMaxPeers + 1];   // per rank: j-side sums of ITS bodies (float4 per local body); mine is local memory,
-                                  // the others are NVLink peer memory; accumulated with atomics, zero before the pass
+    long long* accj[kMaxPeers + 1];   // per rank: j-side sums of ITS bodies, 3 x kFxLimbs words of wide fixed point per
+                                      // local body (gs_device.cuh, fx_add), stored per j-tile as [component][limb][body];
+                                      // mine is local memory, the others NVLink peer memory; exact integer atomics,
+                                      // all zero before the pass
     const SymCta* ctas;      // [grid]
     int n, i_begin;          // real bodies; first body of this rank's slice
     int ni_tiles;            // rows = i-tiles of this rank's slice

@@ -20,7 +20,11 @@
 //     Nothing in it has to be zero beforehand: each call overwrites exactly the entries it reads
 //     back, so leftovers from an earlier (larger) call are never seen;
 //   * the first call on each device looks the array's device address up (cudaGetSymbolAddress)
-//     and remembers it.  Make that first call during set-up, before starting any stream capture.
+//     and remembers it.  Make that first call during set-up, before starting any stream capture;
+//   * "each device" means the CURRENT device of the calling thread: the scratch used is the copy
+//     that lives on it, so pos_packed_dev, potential_dev and the stream must all belong to the
+//     current device (cudaSetDevice first when the process drives several GPUs).  The call checks
+//     this for the two pointers and refuses (GS_EINVAL) rather than touch another GPU's array.
 // The call itself only launches two kernels on the given stream: no cudaMalloc, no cudaFree, no
 // library routine that allocates, no host synchronisation.
 #include <mutex>
@@ -85,11 +89,20 @@ extern "C" int gs_potential_energy_noalloc(const void* pos_packed_dev, int n_pad
     double* scratch = nullptr;
     const int rc = scratch_address(&scratch);
     if (rc != GS_OK) return rc;
+    // the scratch just resolved lives on the current device: both buffers have to live there too
+    int dev = -1;
+    cudaGetDevice(&dev);
+    const void* ptrs[2] = {pos_packed_dev, potential_dev};
+    for (const void* q : ptrs) {
+        cudaPointerAttributes at;
+        if (cudaPointerGetAttributes(&at, q) != cudaSuccess) { cudaGetLastError(); return GS_EINVAL; }
+        if (at.type != cudaMemoryTypeDevice || at.device != dev) return GS_EINVAL;
+    }
     cudaStream_t s = (cudaStream_t)stream;
     const float eps2 = (float)(eps * eps);
     const float cut2 = (eps > 0.0) ? 0.f : 1e-20f;             // same pair rule as gs_energy
     if (gs::launch_potential((const float4*)pos_packed_dev, n_pad, 0, n_pad, eps2, cut2, scratch, s) != cudaSuccess)
         return GS_ECUDA;
     noalloc_reduce_kernel<<<1, 256, 0, s>>>(scratch, n_pad / kPartialBodies, -0.5 / G, potential_dev);
-    return cudaGetLastError() == cudaSuccess ? GS_OK : GS_ECUDA;
+    return cudaPeekAtLastError() == cudaSuccess ? GS_OK : GS_ECUDA;     // this launch only; earlier sticky errors are the caller's
 }

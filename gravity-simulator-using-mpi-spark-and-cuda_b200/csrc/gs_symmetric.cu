@@ -27,6 +27,7 @@
 
 namespace gs {
 
+static_assert(kSymAccjBytesPerBody == kFxWordsPerBody * (int)sizeof(long long), "accj sizing");
 constexpr int kSymDefaultNPair = 4;
 constexpr size_t kSymTileBytes = (size_t)kJTile * sizeof(float4);
 constexpr size_t kSymAccBytesPerWarp = (size_t)(kJTile / 2) * (sizeof(float4) + sizeof(float2));
@@ -264,31 +265,38 @@ __global__ void __launch_bounds__(THREADS, 1) sym_force_kernel(const SymParams p
                 __syncthreads();
                 const int jtile = sym_unit_tile(p, row, kk);
                 const int owner = jtile / p.slice_tiles;                   // whose bodies these are: local or NVLink peer memory
-                float* const jbase = p.accj[owner] + 4 * (size_t)(jtile - owner * p.slice_tiles) * kJTile;
+                // accj layout: per j-tile, word (component * kFxLimbs + limb) * kJTile + body: consecutive lanes =
+                // consecutive bodies = consecutive words, so each of the integer atomics below is one coalesced request
+                long long* const jbase = p.accj[owner] + (size_t)kFxWordsPerBody * (size_t)(jtile - owner * p.slice_tiles) * kJTile;
                 const float w = UNI ? -p.mu_uniform : 1.f;
-                for (int e = tid; e < kJTile / 2; e += THREADS) {
-                    float4 SA = make_float4(0.f, 0.f, 0.f, 0.f);
-                    float2 SB = make_float2(0.f, 0.f);
+                for (int body = tid; body < kJTile; body += THREADS) {
+                    const int e = body >> 1;
+                    const bool odd = (body & 1) != 0;
+                    float sx = 0.f, sy = 0.f, sz = 0.f;
 #pragma unroll
                     for (int wv = 0; wv < WARPS; ++wv) {
                         const float4 a = accA_all[wv * (kJTile / 2) + e];
                         const float2 b = accB_all[wv * (kJTile / 2) + e];
-                        SA.x += a.x; SA.y += a.y; SA.z += a.z; SA.w += a.w; SB.x += b.x; SB.y += b.y;
-                        if (!SHFL) {
-                            accA_all[wv * (kJTile / 2) + e] = make_float4(0.f, 0.f, 0.f, 0.f);
-                            accB_all[wv * (kJTile / 2) + e] = make_float2(0.f, 0.f);
-                        }
+                        sx += odd ? a.y : a.x; sy += odd ? a.w : a.z; sz += odd ? b.y : b.x;
                     }
-                    // System scope: the owner's SMs and every peer's add into the same words, over NVLink for a
-                    // remote owner; only system-scope atomics are guaranteed atomic across GPUs (SASS: RED...SYS).
-                    // On one GPU device scope is enough.
-                    float* dst = jbase + 4 * (2 * e);                          // bodies 2e, 2e+1 of the tile
+                    // Exact fixed-point adds (gs_device.cuh): the owner's j-side sums do not depend on the order in
+                    // which CTAs and GPUs arrive.  System scope when other GPUs add into the same words over NVLink
+                    // (only system-scope atomics are atomic across GPUs; SASS: RED.E.ADD.64...SYS); on one GPU
+                    // device scope is enough.
+                    long long* dst = jbase + body;
                     if (p.world > 1) {
-                        atomicAdd_system(dst + 0, w * SA.x); atomicAdd_system(dst + 1, w * SA.z); atomicAdd_system(dst + 2, w * SB.x);
-                        atomicAdd_system(dst + 4, w * SA.y); atomicAdd_system(dst + 5, w * SA.w); atomicAdd_system(dst + 6, w * SB.y);
+                        fx_add<true>(dst, kJTile, w * sx); fx_add<true>(dst + kFxLimbs * kJTile, kJTile, w * sy);
+                        fx_add<true>(dst + 2 * kFxLimbs * kJTile, kJTile, w * sz);
                     } else {
-                        atomicAdd(dst + 0, w * SA.x); atomicAdd(dst + 1, w * SA.z); atomicAdd(dst + 2, w * SB.x);
-                        atomicAdd(dst + 4, w * SA.y); atomicAdd(dst + 5, w * SA.w); atomicAdd(dst + 6, w * SB.y);
+                        fx_add<false>(dst, kJTile, w * sx); fx_add<false>(dst + kFxLimbs * kJTile, kJTile, w * sy);
+                        fx_add<false>(dst + 2 * kFxLimbs * kJTile, kJTile, w * sz);
+                    }
+                }
+                if (!SHFL) {
+                    __syncthreads();
+                    for (int e = tid; e < WARPS * (kJTile / 2); e += THREADS) {
+                        accA_all[e] = make_float4(0.f, 0.f, 0.f, 0.f);
+                        accB_all[e] = make_float2(0.f, 0.f);
                     }
                 }
                 __syncthreads();
@@ -333,12 +341,23 @@ __global__ void __launch_bounds__(256) sym_finish_kernel(const StepParams p, con
             a1.x += s1.x; a1.y += s1.y; a1.z += s1.z;
         }
     }
-    float4* mine = reinterpret_cast<float4*>(sp.accj[sp.rank]);
-    const float4 j0 = mine[2 * (size_t)pair_local], j1 = mine[2 * (size_t)pair_local + 1];
-    mine[2 * (size_t)pair_local] = make_float4(0.f, 0.f, 0.f, 0.f);        // ready for the next pass
-    mine[2 * (size_t)pair_local + 1] = make_float4(0.f, 0.f, 0.f, 0.f);
-    a0.x += j0.x; a0.y += j0.y; a0.z += j0.z;
-    a1.x += j1.x; a1.y += j1.y; a1.z += j1.z;
+    const int body0 = 2 * pair_local;                                    // local bodies body0, body0 + 1
+    long long* mine = sp.accj[sp.rank] + (size_t)kFxWordsPerBody * (size_t)(body0 / kJTile) * kJTile + (body0 % kJTile);
+    float j[6];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        long long l0[kFxLimbs], l1[kFxLimbs];
+#pragma unroll
+        for (int k = 0; k < kFxLimbs; ++k) {
+            longlong2* w = reinterpret_cast<longlong2*>(mine + (size_t)(c * kFxLimbs + k) * kJTile);
+            const longlong2 v = *w;
+            l0[k] = v.x; l1[k] = v.y;
+            *w = make_longlong2(0, 0);                                     // ready for the next pass
+        }
+        j[c] = fx_value(l0); j[3 + c] = fx_value(l1);
+    }
+    a0.x += j[0]; a0.y += j[1]; a0.z += j[2];
+    a1.x += j[3]; a1.y += j[4]; a1.z += j[5];
     finish_pair<true>(p, pair_local, a0, a1, &ex);
 }
 

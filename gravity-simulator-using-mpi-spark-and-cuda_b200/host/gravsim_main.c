@@ -131,11 +131,14 @@ int main(int argc, char **argv) {
     float *result = (float *)malloc(sizeof(float) * 7 * (size_t)o.n);
     if (!bodies || !result) { fprintf(stderr, "gravsim: out of host memory\n"); return 1; }
     int rc = GS_OK;
+    int64_t step0 = 0;          /* resume: the clock of the input state carries over into the output */
+    double time0 = 0.0;
     if (o.in_path) {
         gs_state_header h;
         rc = gs_state_read_header(o.in_path, &h);
         if (rc == GS_OK && (h.n != o.n || h.record_bytes != 28)) rc = GS_EINVAL;
         if (rc == GS_OK) rc = gs_state_read(o.in_path, &h, bodies, sizeof(float) * 7 * (size_t)o.n);
+        if (rc == GS_OK) { step0 = h.step; time0 = h.time; }
     } else if (!strcmp(o.ic, "plummer")) rc = gs_ic_plummer_f32(bodies, o.n, o.seed, 10.0);
     else if (!strcmp(o.ic, "galaxies")) rc = gs_ic_two_galaxy_f32(bodies, o.n, o.seed, 8.0, 2.0, 0.5);
     else rc = gs_ic_reference_uniform_f32(bodies, o.n, o.seed);
@@ -184,7 +187,7 @@ int main(int argc, char **argv) {
     if (o.out_path) {
         gs_state_header h;
         memset(&h, 0, sizeof(h));
-        h.n = o.n; h.record_bytes = 28; h.step = o.steps; h.time = o.steps * o.dt; h.dt = o.dt; h.G = o.G; h.eps = o.eps;
+        h.n = o.n; h.record_bytes = 28; h.step = step0 + o.steps; h.time = time0 + o.steps * o.dt; h.dt = o.dt; h.G = o.G; h.eps = o.eps;
         if ((rc = gs_state_write(o.out_path, &h, result)) != GS_OK) {
             fprintf(stderr, "gravsim: writing %s: %s\n", o.out_path, gs_strerror(rc));
             return 1;

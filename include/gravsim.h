@@ -167,7 +167,9 @@ int gs_energy(gs_ctx *ctx, double *kinetic, double *potential, double momentum[3
  *   - n_pad <= GS_NOALLOC_MAX_BODIES, else GS_ETOOBIG and nothing is launched;
  *   - every call on a GPU shares that array: calls that can overlap on the GPU (two streams, two
  *     threads) race and must be serialised by the caller; stale contents are never read;
- *   - the first call on each device resolves the array's address; make it before any stream capture.
+ *   - the first call on each device resolves the array's address; make it before any stream capture;
+ *   - the array used is the CURRENT device's copy: pos_packed_dev, potential_dev and `stream` must belong to
+ *     the current device (cudaSetDevice first); pointers of another device are refused with GS_EINVAL.
  * pos_packed_dev: n_pad bodies in the packed-pair layout of DESIGN.md section 3, caller-owned device
  * memory ({x0,x1,y0,y1},{z0,z1,mu0,mu1} per pair, mu = (float)(G*mass); bodies beyond the real ones
  * all-zero); n_pad a multiple of 512.  potential_dev: one double in device memory, written on

@@ -224,6 +224,22 @@ def test_symmetric_pass(gs, oracle, grid, monkeypatch):
             assert floor_err(gpu_accel(gs, p, G=1.0, eps=0.02, flags=flags, variant=variant), ref, ns).max() <= ACC_TOL
 
 
+def test_default_pass_is_bit_reproducible(gs):
+    # j-side sums are accumulated as exact wide fixed point (integer atomics): the order in which CTAs arrive
+    # cannot change the result, so two runs of the default pair-symmetric pass agree bit for bit
+    for n, make, kw in ((70001, gs.ic_reference_uniform, {}), (300000, gs.ic_plummer, dict(G=1.0, eps=0.01, dt=1.0 / 256))):
+        b = make(n, seed=9)
+        outs = []
+        for _ in range(2):
+            with gs.GravSim(n, variant=3, **kw) as sim:
+                assert sim.info.symmetric == 1
+                sim.upload(b)
+                a = sim.accel()
+                sim.step(3)
+                outs.append((a, sim.download()))
+        assert np.array_equal(outs[0][0], outs[1][0]) and np.array_equal(outs[0][1], outs[1][1])
+
+
 # ---- integration ------------------------------------------------------------------------------------
 def _traj_err(out, ref):
     pos = np.abs(out[:, :3].astype(np.float64) - ref[:, :3]).max() / np.abs(ref[:, :3]).max()
@@ -415,6 +431,14 @@ def test_cli_driver_end_to_end(gs, oracle, tmp_path):
     assert h.step == 10 and np.abs(state[:, :3] - ref[:, :3]).max() <= 2e-6 * 3e11
     line = [l for l in r.stdout.splitlines() if l.startswith("Particle 1:")][0]
     assert line == "Particle 1: (%.14f, %.14f, %.14f)" % tuple(state[1, :3])
+    # resume from the checkpoint: 10 + 5 steps == 15 steps, and the step counter / clock carry over
+    out2, out3 = str(tmp_path / "resumed.gs"), str(tmp_path / "straight.gs")
+    for cmd in ([exe, "1500", "5", "3600", "--in", out, "--out", out2, "--quiet"],
+                [exe, "1500", "15", "3600", "--seed", "42", "--out", out3, "--quiet"]):
+        assert subprocess.run(cmd, capture_output=True, text=True, timeout=300).returncode == 0
+    (s2, h2), (s3, h3) = gs.state_read(out2), gs.state_read(out3)
+    assert h2.step == 15 and h2.time == 15 * 3600.0 and h3.step == 15
+    assert np.abs(s2[:, :3] - s3[:, :3]).max() <= 1e-6 * 3e11
 
 
 def test_cli_driver_two_gpus_when_present(gs, oracle, tmp_path):
@@ -483,6 +507,7 @@ def test_multi_gpu_symmetric_pass(gs, oracle, W):
     b, a = _one_step_accel(gs, p, W, 1.0 / 256, G=1.0, eps=0.01, variant=3)
     ref, ns = oracle.accel_subset(b.astype(np.float64), np.arange(n), G=1.0, eps=0.01, massfree=True)
     assert floor_err(a, ref, ns).max() <= ACC_TOL
+    assert np.array_equal(a, _one_step_accel(gs, p, W, 1.0 / 256, G=1.0, eps=0.01, variant=3)[1])   # bit-reproducible
     # (2) the reference's own law and distribution: general masses, eps = 0 (tracked cutoff), SI units, with a
     # coincident pair and a sub-cutoff pair whose members belong to different ranks
     u = gs.ic_reference_uniform(n, seed=50 + W)

@@ -6,7 +6,8 @@ synchronisation is not acceptable, or they run at the memory limit): its scratch
 __device__ array inside the library instead of a cudaMalloc'ed buffer.  Here it is driven the way
 such a caller would: every device buffer is owned by the test (torch tensors), the library only
 gets raw pointers.  It has to agree with the allocating entry point, gs_energy(), on two calls in a
-row -- the second one smaller than the first, so leftovers in the shared scratch would show."""
+row -- the second one smaller than the first, so leftovers in the shared scratch would show -- and,
+directly, with the fp64 oracle's potential energy."""
 import numpy as np
 import pytest
 
@@ -30,7 +31,7 @@ def pack_pairs(bodies, G):
     return out, n_pad
 
 
-def test_noalloc_potential_matches_gs_energy_twice_in_a_row(gs):
+def test_noalloc_potential_matches_gs_energy_twice_in_a_row(gs, oracle):
     import torch
     cases = [(gs.ic_reference_uniform(5000, seed=41), gs.G_SI, 0.0),      # SI units, cutoff rule
              (gs.ic_plummer(1500, seed=42), 1.0, 0.05)]                   # smaller, softened: stale scratch would show
@@ -51,6 +52,8 @@ def test_noalloc_potential_matches_gs_energy_twice_in_a_row(gs):
         got.append(float(out.item()))
     for g, w in zip(got, want):
         assert np.isfinite(g) and abs(g / w - 1.0) <= PE_TOL, (got, want)
+    for g, (bodies, G, eps) in zip(got, cases):                           # and against the oracle itself
+        assert abs(g / oracle.energy(bodies.astype(np.float64), G=G, eps=eps)[1] - 1.0) <= PE_TOL
 
 
 def test_noalloc_rejects_what_does_not_fit(gs):
@@ -63,4 +66,8 @@ def test_noalloc_rejects_what_does_not_fit(gs):
     assert e.value.code == -8 and "4194304" in str(e.value)               # GS_ETOOBIG, with the limit spelled out
     with pytest.raises(gs.GravSimError) as e:
         gs.potential_energy_noalloc(pos.data_ptr(), 500, 1.0, 0.0, out.data_ptr())   # not a multiple of 512
+    assert e.value.code == -1
+    host = np.zeros(2048, dtype=np.float32)                               # not memory of the current device
+    with pytest.raises(gs.GravSimError) as e:
+        gs.potential_energy_noalloc(host.ctypes.data, 512, 1.0, 0.0, out.data_ptr())
     assert e.value.code == -1
