@@ -12,5 +12,5 @@ from .api import (  # noqa: F401
     ic_reference_uniform, ic_plummer, ic_two_galaxy, plan_slice, plan_cta_range,
     plan_tile_owners, plan_tiles, plan_sym_row, plan_sym_unit, plan_sym_cta, nccl_unique_id, state_write, state_read,
     dump_positions_cuda_format, dump_positions_mpi_format, EXPORTED_SYMBOLS,
-    INTEGRATOR_EULER, INTEGRATOR_LEAPFROG, G_SI, FLAG_TWO_PASS, FLAG_NO_UNIFORM_MASS, FLAG_OVERLAP, FLAG_NCCL_EXCHANGE, FLAG_COMPENSATED, FLAG_DETERMINISTIC, potential_energy_noalloc, NOALLOC_MAX_BODIES,
+    INTEGRATOR_EULER, INTEGRATOR_LEAPFROG, G_SI, FLAG_TWO_PASS, FLAG_NO_UNIFORM_MASS, FLAG_OVERLAP, FLAG_NCCL_EXCHANGE, FLAG_COMPENSATED, FLAG_DETERMINISTIC, FLAG_FP64_FORCES, potential_energy_noalloc, NOALLOC_MAX_BODIES,
 )

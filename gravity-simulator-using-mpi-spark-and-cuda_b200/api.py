@@ -23,6 +23,7 @@ FLAG_OVERLAP = 8
 FLAG_NCCL_EXCHANGE = 16
 FLAG_COMPENSATED = 32
 FLAG_DETERMINISTIC = 128
+FLAG_FP64_FORCES = 256
 NCCL_ID_BYTES = 128
 
 # every symbol include/gravsim.h declares (checked by the CPU tests)
@@ -30,7 +31,7 @@ EXPORTED_SYMBOLS = [
     "gs_config_init", "gs_create", "gs_destroy", "gs_nccl_unique_id",
     "gs_upload_aos_f32", "gs_upload_aos_f64", "gs_download_aos_f32", "gs_download_aos_f64",
     "gs_upload_slice_f32", "gs_upload_slice_f64", "gs_download_slice_f32", "gs_download_slice_f64",
-    "gs_step", "gs_step_trajectory", "gs_accel", "gs_energy", "gs_potential_energy_noalloc", "gs_sync", "gs_set_dt",
+    "gs_step", "gs_step_trajectory", "gs_accel", "gs_accel_f64", "gs_energy", "gs_monitor_start", "gs_monitor_read", "gs_potential_energy_noalloc", "gs_sync", "gs_set_dt",
     "gs_get_info", "gs_kernel_launches", "gs_last_cuda_error", "gs_strerror", "gs_version",
     "gs_host_alloc", "gs_host_free",
     "gs_plan_slice", "gs_plan_cta_range", "gs_plan_tile_owners", "gs_plan_tiles",
@@ -123,7 +124,10 @@ def lib():
     L.gs_step.argtypes = [C.c_void_p, C.c_int]
     L.gs_step_trajectory.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.POINTER(C.c_int)]
     L.gs_accel.argtypes = [C.c_void_p, C.c_void_p]
+    L.gs_accel_f64.argtypes = [C.c_void_p, C.c_void_p]
     L.gs_energy.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    L.gs_monitor_start.argtypes = [C.c_void_p, C.c_int, C.c_int]
+    L.gs_monitor_read.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.POINTER(C.c_int)]
     L.gs_sync.argtypes = [C.c_void_p]
     L.gs_potential_energy_noalloc.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_double, C.c_void_p, C.c_void_p]
     L.gs_set_dt.argtypes = [C.c_void_p, C.c_double]
@@ -395,11 +399,31 @@ class GravSim:
         _check(lib().gs_accel(self._ctx, out.ctypes.data), "gs_accel", self._ctx)
         return out
 
+    def accel_f64(self):
+        """The same as float64 (hi + lo words: beyond fp32 only with FLAG_FP64_FORCES)."""
+        n_local = self.info.i_end - self.info.i_begin
+        out = np.empty((max(n_local, 0), 3), dtype=np.float64)
+        _check(lib().gs_accel_f64(self._ctx, out.ctypes.data), "gs_accel_f64", self._ctx)
+        return out
+
     def energy(self):
         ke, pe = C.c_double(), C.c_double()
         mom = (C.c_double * 3)()
         _check(lib().gs_energy(self._ctx, C.byref(ke), C.byref(pe), mom), "gs_energy", self._ctx)
         return ke.value, pe.value, np.array(list(mom))
+
+    def monitor_start(self, every, capacity=1024):
+        """Sample energy and momentum on the device after every `every`-th step (0 = off)."""
+        _check(lib().gs_monitor_start(self._ctx, int(every), int(capacity)), "gs_monitor_start", self._ctx)
+        self._mon_capacity = int(capacity)
+
+    def monitor_read(self):
+        """(k, 8) float64: step, time, KE, PE, px, py, pz, 0 of the samples taken so far."""
+        cap = getattr(self, "_mon_capacity", 0)
+        out = np.zeros((max(cap, 1), 8))
+        got = C.c_int()
+        _check(lib().gs_monitor_read(self._ctx, out.ctypes.data, cap, C.byref(got)), "gs_monitor_read", self._ctx)
+        return out[:got.value]
 
     def sync(self):
         _check(lib().gs_sync(self._ctx), "gs_sync", self._ctx)

@@ -36,6 +36,7 @@ struct gs_ctx {
     float4* lo_full[2] = {nullptr, nullptr};   // ... gathered for download when world_size > 1 (lazy)
     float4* acc_local = nullptr;  // world_size > 1: accelerations from the local j-slice
     float4* acc_stage = nullptr;  // peer-memory mode: accelerations handed from the force kernel to the finish kernel
+    float4* acc_lo = nullptr;     // GS_FLAG_FP64_FORCES: low-order words of the accelerations
     float4* acc_out = nullptr;    // gs_accel output (lazy)
     float4* partial = nullptr;    // split-tile scratch
     size_t partial_bytes = 0;
@@ -58,6 +59,10 @@ struct gs_ctx {
     uint64_t launches = 0;
     int last_cuda_error = 0;
     int64_t steps_done = 0;
+    double sim_time = 0.0;        // sum of the dt of the steps since the last upload
+    // on-device energy / momentum monitor (gs_monitor_start): samples stay in device memory until read
+    double* d_log = nullptr;
+    int mon_every = 0, mon_capacity = 0, mon_count = 0;
     bool split_full = false, split_local = false, split_remote = false;   // does a pass need the fix-up kernel
     // peer-memory exchange (world_size > 1, all peers mappable): see setup_peer_exchange()
     bool p2p = false;
@@ -170,6 +175,7 @@ int force_pass(gs_ctx* c, int final_mode, float kick, float drift, float4* acc_o
     extras.peers.n = 0;
     extras.pos_lo = c->pos_lo;
     extras.vel_lo = c->vel_lo;
+    extras.acc_lo = nullptr;
     if (c->p2p && final_mode == kFinalIntegrate) {   // fused exchange: the finish kernel stores into every peer's pos[nxt]
         for (int q = 0; q < W; ++q)
             if (q != c->cfg.rank) extras.peers.pos_new[extras.peers.n++] = c->peer_pos[c->cur ^ 1][q];
@@ -195,6 +201,24 @@ int force_pass(gs_ctx* c, int final_mode, float kick, float drift, float4* acc_o
         }
         return GS_OK;
     };
+    if (c->cfg.flags & GS_FLAG_FP64_FORCES) {
+        // accuracy mode: every ordered pair in fp64 (mpi.c:59-73's precision), then the common finishing kernel
+        if ((rc = wait_positions(c)) != GS_OK) return rc;
+        p.nj_tiles = p.nj_total; p.j_rot = 0;
+        p.acc_in = nullptr; p.acc_out = acc_out; p.final_mode = final_mode;
+        const float4* lo_all = (W == 1) ? c->pos_lo : nullptr;     // low-order words of all bodies are only here on one GPU
+        if (!c->mass_full) {     // after a slice upload every rank only holds its own masses
+            if (nccl_api().AllGather(c->mass + c->i_begin, c->mass, (size_t)c->slice, ncclDouble, c->comm, c->stream) != ncclSuccess)
+                return GS_ENCCL;
+            c->mass_full = true;
+        }
+        GS_CUDA(c, launch_force_f64(c->pos[c->cur], lo_all, c->mass, c->cfg.G, c->n_pad, c->i_begin, c->slice, c->cfg.eps * c->cfg.eps,
+                                    c->cfg.eps > 0.0 ? 0.0 : 1e-20, c->acc_stage, c->acc_lo, c->stream));
+        extras.acc_lo = c->acc_lo;
+        GS_CUDA(c, launch_finish_acc(p, c->slice, c->acc_stage, &extras, c->stream));
+        c->launches += 2;
+        return GS_OK;
+    }
     if (!two_pass) {
         if ((rc = wait_positions(c)) != GS_OK) return rc;
         p.nj_tiles = p.nj_total; p.j_rot = 0;
@@ -614,8 +638,8 @@ void gs_destroy(gs_ctx* c) {
     cudaFree(c->pos[0]); cudaFree(c->pos[1]); cudaFree(c->vel); cudaFree(c->vel_full);
     cudaFree(c->d_sym_ctas); cudaFree(c->d_sym_rows); cudaFree(c->d_accj); cudaFree(c->sym_partial);
     cudaFree(c->pos_lo); cudaFree(c->vel_lo); cudaFree(c->lo_full[0]); cudaFree(c->lo_full[1]);
-    cudaFree(c->acc_local); cudaFree(c->acc_stage); cudaFree(c->acc_out); cudaFree(c->partial); cudaFree(c->mass);
-    cudaFree(c->d_aos); cudaFree(c->d_energy); cudaFree(c->d_mu_mm);
+    cudaFree(c->acc_local); cudaFree(c->acc_stage); cudaFree(c->acc_lo); cudaFree(c->acc_out); cudaFree(c->partial); cudaFree(c->mass);
+    cudaFree(c->d_aos); cudaFree(c->d_energy); cudaFree(c->d_mu_mm); cudaFree(c->d_log);
     if (c->h_energy) cudaFreeHost(c->h_energy);
     if (c->h_mu_mm) cudaFreeHost(c->h_mu_mm);
     if (c->h_acc) cudaFreeHost(c->h_acc);
@@ -739,8 +763,11 @@ int gs_create(gs_ctx** out, const gs_config* cfg) {
         (!dmalloc((void**)&c->pos_lo, vel_bytes) || !dmalloc((void**)&c->vel_lo, vel_bytes) ||
          (!c->acc_stage && !dmalloc((void**)&c->acc_stage, vel_bytes))))
         return fail(GS_ENOMEM);
+    if ((c->cfg.flags & GS_FLAG_FP64_FORCES) &&
+        ((!c->acc_stage && !dmalloc((void**)&c->acc_stage, vel_bytes)) || !dmalloc((void**)&c->acc_lo, vel_bytes)))
+        return fail(GS_ENOMEM);
     // pair-symmetric pass: wanted unless the caller asks for bit-reproducible sums; needs a 256-thread R=4/6 variant
-    c->want_sym = !(c->cfg.flags & GS_FLAG_DETERMINISTIC) && sym_supported(c->R, c->threads) &&
+    c->want_sym = !(c->cfg.flags & (GS_FLAG_DETERMINISTIC | GS_FLAG_FP64_FORCES)) && sym_supported(c->R, c->threads) &&
                   cfg->world_size <= kMaxPeers + 1;
     if (c->want_sym) {      // allocated now so that setup_peer_exchange() can publish it to the peers
         const size_t accj_bytes = (size_t)c->slice * kSymAccjBytesPerBody;
@@ -806,6 +833,8 @@ static int reset_after_upload(gs_ctx* c) {
     c->uploaded = true;
     c->vel_synced = true;
     c->steps_done = 0;
+    c->sim_time = 0.0;
+    c->mon_count = 0;
     return GS_OK;
 }
 
@@ -902,6 +931,8 @@ static int upload_slice_common(gs_ctx* c, const void* host, int first, int count
 int gs_upload_slice_f32(gs_ctx* ctx, const void* my28, int first, int count) { return upload_slice_common(ctx, my28, first, count, 28); }
 int gs_upload_slice_f64(gs_ctx* ctx, const void* my56, int first, int count) { return upload_slice_common(ctx, my56, first, count, 56); }
 
+static int energy_enqueue(gs_ctx* c, double* out8);
+
 static int one_step(gs_ctx* c) {
     int rc;
     const float dt = (float)c->cfg.dt;
@@ -917,6 +948,12 @@ static int one_step(gs_ctx* c) {
     c->cur = nxt;
     if (c->cfg.integrator == GS_INTEGRATOR_LEAPFROG) c->vel_synced = false;
     c->steps_done++;
+    c->sim_time += c->cfg.dt;
+    if (c->mon_every > 0 && c->steps_done % c->mon_every == 0 && c->mon_count < c->mon_capacity) {
+        // the sample is computed and stored on the device; with the leapfrog this closes the half kick first
+        if ((rc = energy_enqueue(c, c->d_log + (size_t)8 * c->mon_count)) != GS_OK) return rc;
+        c->mon_count++;
+    }
     return GS_OK;
 }
 
@@ -994,32 +1031,63 @@ int gs_step_trajectory(gs_ctx* c, int nsteps, int every, float* xyz_host, int ca
     return taken > 0 ? check_peers(c) : GS_OK;        // the frames were synchronised above
 }
 
-int gs_accel(gs_ctx* c, float* acc3_host) {
-    if (!c || !acc3_host) return GS_EINVAL;
+static int accel_common(gs_ctx* c, float* acc3_f32, double* acc3_f64) {
+    if (!c || (!acc3_f32 && !acc3_f64)) return GS_EINVAL;
     if (!c->uploaded) return GS_ESTATE;
     int rc = set_device(c);
     if (rc != GS_OK) return rc;
     const size_t bytes = (size_t)c->slice * sizeof(float4);
     if (!c->acc_out) GS_CUDA(c, cudaMalloc((void**)&c->acc_out, bytes));
-    if (c->h_acc_bytes < bytes) {
+    if (c->h_acc_bytes < 2 * bytes) {
         if (c->h_acc) cudaFreeHost(c->h_acc);
         c->h_acc = nullptr; c->h_acc_bytes = 0;
-        GS_CUDA(c, cudaHostAlloc((void**)&c->h_acc, bytes, cudaHostAllocDefault));
-        c->h_acc_bytes = bytes;
+        GS_CUDA(c, cudaHostAlloc((void**)&c->h_acc, 2 * bytes, cudaHostAllocDefault));
+        c->h_acc_bytes = 2 * bytes;
     }
     if ((rc = force_pass(c, kFinalAccOut, 0.f, 0.f, c->acc_out)) != GS_OK) return rc;
     int n_local = c->n - c->i_begin;
     if (n_local > c->slice) n_local = c->slice;
     if (n_local < 0) n_local = 0;
+    const bool have_lo = (c->cfg.flags & GS_FLAG_FP64_FORCES) != 0;
     GS_CUDA(c, cudaMemcpyAsync(c->h_acc, c->acc_out, (size_t)n_local * sizeof(float4), cudaMemcpyDeviceToHost,
                                c->stream));
+    if (have_lo)
+        GS_CUDA(c, cudaMemcpyAsync(c->h_acc + c->slice, c->acc_lo, (size_t)n_local * sizeof(float4), cudaMemcpyDeviceToHost,
+                                   c->stream));
     GS_CUDA(c, cudaStreamSynchronize(c->stream));
     if ((rc = check_peers(c)) != GS_OK) return rc;
     for (int i = 0; i < n_local; ++i) {
-        acc3_host[3 * (size_t)i + 0] = c->h_acc[i].x;
-        acc3_host[3 * (size_t)i + 1] = c->h_acc[i].y;
-        acc3_host[3 * (size_t)i + 2] = c->h_acc[i].z;
+        const float4 h = c->h_acc[i];
+        const float4 l = have_lo ? c->h_acc[c->slice + i] : make_float4(0.f, 0.f, 0.f, 0.f);
+        if (acc3_f32) { acc3_f32[3 * (size_t)i + 0] = h.x; acc3_f32[3 * (size_t)i + 1] = h.y; acc3_f32[3 * (size_t)i + 2] = h.z; }
+        if (acc3_f64) {
+            acc3_f64[3 * (size_t)i + 0] = (double)h.x + l.x; acc3_f64[3 * (size_t)i + 1] = (double)h.y + l.y;
+            acc3_f64[3 * (size_t)i + 2] = (double)h.z + l.z;
+        }
     }
+    return GS_OK;
+}
+
+int gs_accel(gs_ctx* c, float* acc3_host) { return accel_common(c, acc3_host, nullptr); }
+int gs_accel_f64(gs_ctx* c, double* acc3_host) { return accel_common(c, nullptr, acc3_host); }
+
+// Enqueues one energy / momentum sample into out8 (device memory, 8 doubles: step, time, KE, PE, px, py, pz, 0):
+// potential pass (O(N^2), fp32 pair terms, fp64 sums), kinetic pass, device-side reduction and, on several GPUs, an
+// in-place ncclAllReduce of the five sums.  No host synchronisation, no host arithmetic.
+static int energy_enqueue(gs_ctx* c, double* out8) {
+    int rc;
+    if ((rc = sync_velocities(c)) != GS_OK) return rc;
+    if ((rc = wait_positions(c)) != GS_OK) return rc;
+    const int egrid = energy_grid(c->slice);
+    double* d_pot = c->d_energy;
+    double* d_kin = c->d_energy + egrid;
+    GS_CUDA(c, launch_potential(c->pos[c->cur], c->n_pad, c->i_begin, c->slice, c->eps2, c->cut2, d_pot, c->stream));
+    GS_CUDA(c, launch_kinetic(c->vel, c->mass, c->i_begin, c->slice, d_kin, c->stream));
+    GS_CUDA(c, launch_energy_sample(d_pot, d_kin, egrid, c->cfg.G, (double)c->steps_done, c->sim_time, out8, c->stream));
+    c->launches += 3;
+    if (c->cfg.world_size > 1 &&
+        nccl_api().AllReduce(out8 + 2, out8 + 2, 5, ncclDouble, ncclSum, c->comm, c->stream) != ncclSuccess)
+        return GS_ENCCL;
     return GS_OK;
 }
 
@@ -1028,39 +1096,40 @@ int gs_energy(gs_ctx* c, double* kinetic, double* potential, double momentum[3])
     if (!c->uploaded) return GS_ESTATE;
     int rc = set_device(c);
     if (rc != GS_OK) return rc;
-    if ((rc = sync_velocities(c)) != GS_OK) return rc;
-    if ((rc = wait_positions(c)) != GS_OK) return rc;
-    const int egrid = energy_grid(c->slice);
-    double* d_pot = c->d_energy;
-    double* d_kin = c->d_energy + egrid;
-    double* d_red = c->d_energy + (size_t)egrid * 5;
-    GS_CUDA(c, launch_potential(c->pos[c->cur], c->n_pad, c->i_begin, c->slice, c->eps2, c->cut2, d_pot, c->stream));
-    GS_CUDA(c, launch_kinetic(c->vel, c->mass, c->i_begin, c->slice, d_kin, c->stream));
-    c->launches += 2;
-    GS_CUDA(c, cudaMemcpyAsync(c->h_energy, c->d_energy, (size_t)egrid * 5 * sizeof(double), cudaMemcpyDeviceToHost,
-                               c->stream));
+    double* d_out = c->d_energy + (size_t)energy_grid(c->slice) * 5;
+    if ((rc = energy_enqueue(c, d_out)) != GS_OK) return rc;
+    GS_CUDA(c, cudaMemcpyAsync(c->h_energy, d_out, 8 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
     GS_CUDA(c, cudaStreamSynchronize(c->stream));
     if ((rc = check_peers(c)) != GS_OK) return rc;
-    double v[5] = {0, 0, 0, 0, 0};   // {sum mu_i phi_i, sum m v^2, px, py, pz}
-    for (int b = 0; b < egrid; ++b) {
-        v[0] += c->h_energy[b];
-        for (int k = 0; k < 4; ++k) v[1 + k] += c->h_energy[egrid + 4 * b + k];
-    }
-    if (c->cfg.world_size > 1) {
-        NcclApi& nc = nccl_api();
-        double* h_red = c->h_energy + (size_t)egrid * 5;
-        memcpy(h_red, v, sizeof(v));
-        GS_CUDA(c, cudaMemcpyAsync(d_red, h_red, sizeof(v), cudaMemcpyHostToDevice, c->stream));
-        if (nc.AllReduce(d_red, d_red, 5, ncclDouble, ncclSum, c->comm, c->stream) != ncclSuccess) return GS_ENCCL;
-        GS_CUDA(c, cudaMemcpyAsync(h_red, d_red, sizeof(v), cudaMemcpyDeviceToHost, c->stream));
-        GS_CUDA(c, cudaStreamSynchronize(c->stream));
-        memcpy(v, h_red, sizeof(v));
-    }
-    // U = -sum_{i<j} G m_i m_j / d = -(1/(2G)) sum_i mu_i sum_{j!=i} mu_j / d
-    if (potential) *potential = -0.5 * v[0] / c->cfg.G;
-    if (kinetic) *kinetic = 0.5 * v[1];
-    if (momentum) { momentum[0] = v[2]; momentum[1] = v[3]; momentum[2] = v[4]; }
+    if (kinetic) *kinetic = c->h_energy[2];
+    if (potential) *potential = c->h_energy[3];
+    if (momentum) { momentum[0] = c->h_energy[4]; momentum[1] = c->h_energy[5]; momentum[2] = c->h_energy[6]; }
     return GS_OK;
+}
+
+int gs_monitor_start(gs_ctx* c, int every, int capacity) {
+    if (!c || every < 0 || capacity < 0) return GS_EINVAL;
+    int rc = set_device(c);
+    if (rc != GS_OK) return rc;
+    GS_CUDA(c, cudaStreamSynchronize(c->stream));
+    cudaFree(c->d_log);
+    c->d_log = nullptr;
+    c->mon_every = c->mon_capacity = c->mon_count = 0;
+    if (every == 0 || capacity == 0) return GS_OK;           // monitor off
+    GS_CUDA(c, cudaMalloc((void**)&c->d_log, (size_t)capacity * 8 * sizeof(double)));
+    c->mon_every = every; c->mon_capacity = capacity;
+    return GS_OK;
+}
+
+int gs_monitor_read(gs_ctx* c, double* samples8, int capacity, int* count) {
+    if (!c || !count || capacity < 0 || (capacity > 0 && !samples8)) return GS_EINVAL;
+    int rc = set_device(c);
+    if (rc != GS_OK) return rc;
+    const int n = c->mon_count < capacity ? c->mon_count : capacity;
+    if (n > 0) GS_CUDA(c, cudaMemcpyAsync(samples8, c->d_log, (size_t)n * 8 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    GS_CUDA(c, cudaStreamSynchronize(c->stream));
+    *count = n;
+    return check_peers(c);
 }
 
 static int download_common(gs_ctx* c, void* host, int n, int record_bytes) {

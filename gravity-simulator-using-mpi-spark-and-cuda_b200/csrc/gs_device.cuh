@@ -123,11 +123,12 @@ __device__ __forceinline__ void comp_add(float& hi, float& lo, float inc_hi, flo
     hi = __fadd_rn(s, e);
     lo = __fadd_rn(e, -__fadd_rn(hi, -s));
 }
-// v += a*kick ; x += v*drift, both compensated
-__device__ __forceinline__ void comp_step(float a, float kick, float drift, bool do_drift, float& v, float& vlo,
+// v += (a + alo)*kick ; x += v*drift, both compensated (alo: low-order word of the acceleration, 0 unless the forces
+// were summed in fp64)
+__device__ __forceinline__ void comp_step(float a, float alo, float kick, float drift, bool do_drift, float& v, float& vlo,
                                           float& x, float& xlo) {
     const float dv = __fmul_rn(a, kick);
-    comp_add(v, vlo, dv, __fmaf_rn(a, kick, -dv));
+    comp_add(v, vlo, dv, __fmaf_rn(alo, kick, __fmaf_rn(a, kick, -dv)));
     if (!do_drift) return;
     const float dx = __fmul_rn(v, drift);
     comp_add(x, xlo, dx, __fadd_rn(__fmaf_rn(v, drift, -dx), __fmul_rn(vlo, drift)));
@@ -157,12 +158,15 @@ __device__ __forceinline__ void finish_pair(const StepParams& p, int pair_local,
         float4 LA = ex->pos_lo[2 * pair_local], LB = ex->pos_lo[2 * pair_local + 1];
         float4 WA = ex->vel_lo[2 * pair_local], WB = ex->vel_lo[2 * pair_local + 1];
         const bool drift = (p.final_mode != kFinalKickOnly);
-        comp_step(a0.x, p.kick_dt, p.drift_dt, drift, VA.x, WA.x, PA.x, LA.x);
-        comp_step(a1.x, p.kick_dt, p.drift_dt, drift, VA.y, WA.y, PA.y, LA.y);
-        comp_step(a0.y, p.kick_dt, p.drift_dt, drift, VA.z, WA.z, PA.z, LA.z);
-        comp_step(a1.y, p.kick_dt, p.drift_dt, drift, VA.w, WA.w, PA.w, LA.w);
-        comp_step(a0.z, p.kick_dt, p.drift_dt, drift, VB.x, WB.x, PB.x, LB.x);
-        comp_step(a1.z, p.kick_dt, p.drift_dt, drift, VB.y, WB.y, PB.y, LB.y);
+        float4 l0 = make_float4(0.f, 0.f, 0.f, 0.f), l1 = l0;
+        if (ex->acc_lo != nullptr && body0 < p.n) l0 = ex->acc_lo[2 * pair_local];
+        if (ex->acc_lo != nullptr && body0 + 1 < p.n) l1 = ex->acc_lo[2 * pair_local + 1];
+        comp_step(a0.x, l0.x, p.kick_dt, p.drift_dt, drift, VA.x, WA.x, PA.x, LA.x);
+        comp_step(a1.x, l1.x, p.kick_dt, p.drift_dt, drift, VA.y, WA.y, PA.y, LA.y);
+        comp_step(a0.y, l0.y, p.kick_dt, p.drift_dt, drift, VA.z, WA.z, PA.z, LA.z);
+        comp_step(a1.y, l1.y, p.kick_dt, p.drift_dt, drift, VA.w, WA.w, PA.w, LA.w);
+        comp_step(a0.z, l0.z, p.kick_dt, p.drift_dt, drift, VB.x, WB.x, PB.x, LB.x);
+        comp_step(a1.z, l1.z, p.kick_dt, p.drift_dt, drift, VB.y, WB.y, PB.y, LB.y);
         p.vel[2 * pair_local] = VA; p.vel[2 * pair_local + 1] = VB;
         ex->vel_lo[2 * pair_local] = WA; ex->vel_lo[2 * pair_local + 1] = WB;
         if (!drift) return;

@@ -250,8 +250,76 @@ cudaError_t launch_fixup(int variant, const StepParams& p, int grid_main, const 
     const int pairs = p.ni_tiles * (vi.i_tile / 2);
     const int blocks = (pairs + 255) / 256;
     FinishExtras none;
-    none.peers.n = 0; none.pos_lo = nullptr; none.vel_lo = nullptr;
+    none.peers.n = 0; none.pos_lo = nullptr; none.vel_lo = nullptr; none.acc_lo = nullptr;
     fixup_kernel<<<blocks, 256, 0, s>>>(p, grid_main, vi.i_tile, whole_acc, extras ? *extras : none);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------------
+// fp64 force pass (accuracy mode) and the plain finishing kernel
+// ------------------------------------------------------------------------------------------------
+constexpr int kF64Threads = 128;
+
+__global__ void __launch_bounds__(kF64Threads) force_f64_kernel(const float4* __restrict__ pos,
+                                                                const float4* __restrict__ pos_lo_all,
+                                                                const double* __restrict__ mass, double G, int n_pad,
+                                                                int i_begin, double eps2, double cut2,
+                                                                float4* __restrict__ acc_hi, float4* __restrict__ acc_lo) {
+    __shared__ double tx[kJTile], ty[kJTile], tz[kJTile], tmu[kJTile];
+    auto body = [&](int i, double& x, double& y, double& z, double& mu) {
+        const float4 A = pos[2 * (i >> 1)], B = pos[2 * (i >> 1) + 1];
+        const bool odd = (i & 1) != 0;
+        x = odd ? A.y : A.x; y = odd ? A.w : A.z; z = odd ? B.y : B.x;
+        mu = G * mass[i];                        // G*m in fp64 (mpi.c:66), not the fp32 mu of the packed record
+        if (pos_lo_all != nullptr) {
+            const float4 LA = pos_lo_all[2 * (i >> 1)], LB = pos_lo_all[2 * (i >> 1) + 1];
+            x += odd ? LA.y : LA.x; y += odd ? LA.w : LA.z; z += odd ? LB.y : LB.x;
+        }
+    };
+    const int il = blockIdx.x * kF64Threads + threadIdx.x;
+    double xi, yi, zi, mui;
+    body(i_begin + il, xi, yi, zi, mui);
+    double ax = 0.0, ay = 0.0, az = 0.0;
+    for (int j0 = 0; j0 < n_pad; j0 += kJTile) {
+        __syncthreads();
+        for (int t = threadIdx.x; t < kJTile; t += kF64Threads) body(j0 + t, tx[t], ty[t], tz[t], tmu[t]);
+        __syncthreads();
+#pragma unroll 4
+        for (int t = 0; t < kJTile; ++t) {
+            const double dx = tx[t] - xi, dy = ty[t] - yi, dz = tz[t] - zi;
+            const double d2 = dx * dx + dy * dy + dz * dz;
+            const double inv = rsqrt(d2 + eps2);
+            // eps > 0: d = 0 contributes exactly 0; eps == 0: "r < 1e-10 contributes nothing" (mpi.c:64), incl. the body itself
+            const double w = (d2 >= cut2 && tmu[t] != 0.0) ? tmu[t] * inv * inv * inv : 0.0;
+            ax = fma(w, dx, ax); ay = fma(w, dy, ay); az = fma(w, dz, az);
+        }
+    }
+    const float hx = (float)ax, hy = (float)ay, hz = (float)az;
+    acc_hi[il] = make_float4(hx, hy, hz, 0.f);
+    acc_lo[il] = make_float4((float)(ax - hx), (float)(ay - hy), (float)(az - hz), 0.f);
+}
+
+cudaError_t launch_force_f64(const float4* pos, const float4* pos_lo_all, const double* mass, double G, int n_pad,
+                             int i_begin, int n_local_pad, double eps2, double cut2, float4* acc_hi, float4* acc_lo,
+                             cudaStream_t s) {
+    force_f64_kernel<<<n_local_pad / kF64Threads, kF64Threads, 0, s>>>(pos, pos_lo_all, mass, G, n_pad, i_begin, eps2, cut2,
+                                                                      acc_hi, acc_lo);
+    return cudaGetLastError();
+}
+
+__global__ void __launch_bounds__(256) finish_acc_kernel(const StepParams p, int pairs, const float4* __restrict__ acc,
+                                                        const FinishExtras ex) {
+    const int pair_local = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pair_local >= pairs) return;
+    finish_pair<true>(p, pair_local, acc[2 * pair_local], acc[2 * pair_local + 1], &ex);
+}
+
+cudaError_t launch_finish_acc(const StepParams& p, int n_local_pad, const float4* acc, const FinishExtras* extras,
+                              cudaStream_t s) {
+    const int pairs = n_local_pad / 2;
+    FinishExtras none;
+    none.peers.n = 0; none.pos_lo = nullptr; none.vel_lo = nullptr; none.acc_lo = nullptr;
+    finish_acc_kernel<<<(pairs + 255) / 256, 256, 0, s>>>(p, pairs, acc, extras ? *extras : none);
     return cudaGetLastError();
 }
 
@@ -495,6 +563,34 @@ __global__ void __launch_bounds__(kEThreads) kinetic_kernel(const float4* __rest
         out4[4 * blockIdx.x + 0] = e; out4[4 * blockIdx.x + 1] = px;
         out4[4 * blockIdx.x + 2] = py; out4[4 * blockIdx.x + 3] = pz;
     }
+}
+
+// Device-side end of the energy pass: sums the per-CTA partials in a fixed order (bit-reproducible) and writes one
+// sample {step, time, KE, PE, px, py, pz, 0} -- this rank's share; nothing is reduced on the host.
+__global__ void __launch_bounds__(kEThreads) energy_sample_kernel(const double* __restrict__ pot_partials,
+                                                                  const double* __restrict__ kin4, int egrid, double G,
+                                                                  double step, double time, double* __restrict__ out8) {
+    __shared__ double red[kEThreads / 32];
+    double v[5] = {0.0, 0.0, 0.0, 0.0, 0.0};
+    for (int b = threadIdx.x; b < egrid; b += kEThreads) {
+        v[0] += pot_partials[b];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) v[1 + q] += kin4[4 * b + q];
+    }
+    double t[5];
+#pragma unroll
+    for (int q = 0; q < 5; ++q) t[q] = block_sum(v[q], red);
+    if (threadIdx.x == 0) {
+        out8[0] = step; out8[1] = time;
+        out8[2] = 0.5 * t[1];                  // KE = 1/2 sum m v^2
+        out8[3] = -0.5 * t[0] / G;             // U = -(1/(2G)) sum_i mu_i sum_{j != i} mu_j / d
+        out8[4] = t[2]; out8[5] = t[3]; out8[6] = t[4]; out8[7] = 0.0;
+    }
+}
+cudaError_t launch_energy_sample(const double* pot_partials, const double* kin4, int egrid, double G, double step,
+                                 double time, double* out8, cudaStream_t s) {
+    energy_sample_kernel<<<1, kEThreads, 0, s>>>(pot_partials, kin4, egrid, G, step, time, out8);
+    return cudaGetLastError();
 }
 
 int energy_grid(int n_local_pad) { return n_local_pad / kEThreads; }

@@ -50,7 +50,8 @@ struct StepParams {
 struct PeerTargets { int n; float4* pos_new[kMaxPeers]; };
 // What only the finish kernel needs: peers, and the low-order words of the compensated integration
 // (GS_FLAG_COMPENSATED: x = pos + pos_lo, v = vel + vel_lo; null otherwise).  Local (slice) indexing.
-struct FinishExtras { PeerTargets peers; float4* pos_lo; float4* vel_lo; };
+// acc_lo (nullable): low-order words of the accelerations (GS_FLAG_FP64_FORCES), used by the compensated update.
+struct FinishExtras { PeerTargets peers; float4* pos_lo; float4* vel_lo; const float4* acc_lo; };
 
 size_t force_smem_bytes();
 // Max resident CTAs per SM of the force kernel for this variant / cut mode, and its registers.
@@ -61,6 +62,17 @@ cudaError_t launch_force(int variant, int cut_mode, const StepParams& p, int gri
 // whole_acc != nullptr: also finish the whole tiles, whose accelerations the force kernel left there.
 cudaError_t launch_fixup(int variant, const StepParams& p, int grid_main, const float4* whole_acc,
                          const FinishExtras* extras, cudaStream_t s);
+
+// GS_FLAG_FP64_FORCES: accelerations of this rank's bodies summed and evaluated in fp64 (the precision of mpi.c:59-73),
+// one i-body per thread, every ordered pair; positions are pos (+ pos_lo_all when the low-order words of ALL bodies
+// are on this GPU, else nullptr), masses are the original doubles of ALL bodies (mu = G*m in fp64).
+// Output as hi + lo float4 pairs per local body.
+cudaError_t launch_force_f64(const float4* pos, const float4* pos_lo_all, const double* mass, double G, int n_pad,
+                             int i_begin, int n_local_pad, double eps2, double cut2, float4* acc_hi, float4* acc_lo,
+                             cudaStream_t s);
+// Finishes every local pair from accelerations left in `acc` (integration / output / kick, peers, compensated update).
+cudaError_t launch_finish_acc(const StepParams& p, int n_local_pad, const float4* acc, const FinishExtras* extras,
+                              cudaStream_t s);
 
 // Peer-memory exchange (replaces the per-step collective when every GPU can map its peers' buffers):
 // the integrating epilogue stores new positions straight into every peer's position buffer over
@@ -149,5 +161,9 @@ cudaError_t launch_potential(const float4* pos, int n_pad, int i_begin, int n_lo
                              float eps2, float cut2, double* out_partials, cudaStream_t s);
 cudaError_t launch_kinetic(const float4* vel_local, const double* mass, int i_begin, int n_local_pad,
                            double* out4, cudaStream_t s);
+
+// One sample {step, time, KE, PE, px, py, pz, 0} (this rank's share) from the partials, reduced on the device.
+cudaError_t launch_energy_sample(const double* pot_partials, const double* kin4, int egrid, double G, double step,
+                                 double time, double* out8, cudaStream_t s);
 
 }  // namespace gs

@@ -470,7 +470,7 @@ cudaError_t launch_sym_finish(const StepParams& p, const SymParams& sp, const in
                               const FinishExtras* extras, cudaStream_t s) {
     const int pairs = sp.ni_tiles * (i_tile / 2);
     FinishExtras none;
-    none.peers.n = 0; none.pos_lo = nullptr; none.vel_lo = nullptr;
+    none.peers.n = 0; none.pos_lo = nullptr; none.vel_lo = nullptr; none.acc_lo = nullptr;
     sym_finish_kernel<<<(pairs + 255) / 256, 256, 0, s>>>(p, sp, rows, i_tile, extras ? *extras : none);
     return cudaGetLastError();
 }

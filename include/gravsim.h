@@ -78,6 +78,12 @@ typedef struct gs_config {
                                    rounds to the state's fp32 ulp each step (forces stay fp32); f64 records
                                    keep their low-order bits through upload/download                    */
 
+#define GS_FLAG_FP64_FORCES 256u /* accuracy mode: every ordered pair evaluated and summed in fp64, the precision of
+                                   mpi.c:59-73 (positions are the fp32 state, or its hi+lo pairs with
+                                   GS_FLAG_COMPENSATED on one GPU); accelerations reach the integrator as hi+lo fp32
+                                   pairs.  ~8x slower than the default pass; with GS_FLAG_COMPENSATED trajectories
+                                   follow mpi.c's fp64 ones to ~1e-12                                            */
+
 typedef struct gs_info {
     int32_t n, n_pad;             /* bodies, padded bodies (multiple of the tile sizes)          */
     int32_t i_begin, i_end;       /* this rank's i-bodies [i_begin, i_end) clipped to n          */
@@ -152,10 +158,23 @@ int gs_step_trajectory(gs_ctx *ctx, int nsteps, int every, float *xyz_host, int 
  * per body; state unchanged.  The reference only exposes forces[] via the D2H at cuda.cu:160
  * and F/m at cuda.cu:70, mpi.c:206; this is the hook the <=1e-5 parity check consumes. */
 int gs_accel(gs_ctx *ctx, float *acc3_host);
+/* The same as doubles; beyond fp32 only with GS_FLAG_FP64_FORCES (hi + lo words), where it reproduces
+ * sum_j calculate_force()/m_i (mpi.c:199-206) to fp64 rounding. */
+int gs_accel_f64(gs_ctx *ctx, double *acc3_host);
 
 /* Kinetic, potential energy and linear momentum (fp64 accumulation).  Not in the reference.
  * Collective when world_size > 1 (every rank gets the global values). */
 int gs_energy(gs_ctx *ctx, double *kinetic, double *potential, double momentum[3]);
+
+/* On-device energy / momentum monitor (not in the reference, which computes no energies).
+ * After gs_monitor_start, gs_step() takes a sample after every `every`-th step: {step, time, KE, PE, px, py, pz, 0}
+ * (8 doubles), computed, reduced (over the GPU and, with ncclAllReduce, over the ranks) and stored entirely on the
+ * device -- no host synchronisation, no host arithmetic, the step loop stays asynchronous.  At most `capacity` samples
+ * are kept (later ones are dropped); an upload clears them; every = 0 switches the monitor off.  gs_monitor_read
+ * synchronises and copies the samples taken so far.  A sample costs one O(N^2) potential pass, and with the leapfrog a
+ * velocity synchronisation (one extra force pass) -- choose `every` accordingly.  Collective when world_size > 1. */
+int gs_monitor_start(gs_ctx *ctx, int every, int capacity);
+int gs_monitor_read(gs_ctx *ctx, double *samples8, int capacity, int *count);
 
 /* Potential energy WITHOUT any allocation and without a gs_ctx.  (No counterpart in the reference:
  * it computes no energies and allocates as it pleases, cuda.cu:145-149,159.)

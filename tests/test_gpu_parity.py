@@ -335,6 +335,61 @@ def test_compensated_integration_closes_the_fp32_state_gap(gs, oracle):
     assert errs[gs.FLAG_COMPENSATED | gs.FLAG_TWO_PASS][0] <= 2.5e-6
 
 
+def test_fp64_force_mode(gs, oracle):
+    # GS_FLAG_FP64_FORCES: the reference's sound path is fp64 throughout (mpi.c:59-73); this mode evaluates and sums
+    # every ordered pair in fp64.  Accelerations vs the oracle at <= 1e-7 (measured ~1e-13: both are fp64), and with
+    # GS_FLAG_COMPENSATED (hi+lo state) 100 steps of configs[0] follow the fp64 oracle 1000x closer than hi+lo
+    # state with fp32 forces does.
+    F = gs.FLAG_FP64_FORCES
+    for b, kw in ((gs.ic_reference_uniform(4099, seed=17), {}),                       # SI, cutoff rule, padding
+                  (gs.ic_plummer(3000, seed=18), dict(G=1.0, eps=0.02))):
+        b[9] = b[4]                                                                   # coincident pair
+        b[11, 6] = 0.0                                                                # massless body
+        n = b.shape[0]
+        with gs.GravSim(n, flags=F, **kw) as sim:
+            sim.upload(b)
+            a32, a64 = sim.accel(), sim.accel_f64()
+        ref, ns = oracle.accel_subset(b.astype(np.float64), np.arange(n), massfree=True, **kw)
+        assert floor_err(a64, ref, ns).max() <= 1e-12 and rel_err(a64, ref)[np.linalg.norm(ref, axis=1) > 1e-3 * ns].max() <= 1e-10
+        assert floor_err(a32, ref, ns).max() <= 1e-7                                   # one fp32 rounding of the result
+    b = gs.ic_reference_uniform(4096, seed=1234).astype(np.float64)
+    b[3:, :3] += np.random.default_rng(1).uniform(-1000.0, 1000.0, (4093, 3))         # not fp32-representable
+    ref = oracle.run_sync(b, 3600.0, 100)
+    errs = {}
+    for flags in (gs.FLAG_COMPENSATED, gs.FLAG_COMPENSATED | F):
+        with gs.GravSim(4096, dt=3600.0, flags=flags) as sim:
+            sim.upload(b)
+            sim.step(100)
+            errs[flags] = _traj_err(sim.download(np.float64), ref)
+    assert errs[gs.FLAG_COMPENSATED | F][0] <= 1e-3 * errs[gs.FLAG_COMPENSATED][0]
+    assert errs[gs.FLAG_COMPENSATED | F][0] <= 1e-9 and errs[gs.FLAG_COMPENSATED | F][1] <= 1e-8
+
+
+def test_on_device_energy_monitor(gs, oracle):
+    # gs_monitor_start: samples are computed, reduced and stored on the GPU while gs_step stays asynchronous
+    n, eps, dt = 3000, 0.05, 1.0 / 64
+    b = gs.ic_plummer(n, seed=8)
+    for integ in (gs.INTEGRATOR_EULER, gs.INTEGRATOR_LEAPFROG):
+        with gs.GravSim(n, dt=dt, G=1.0, eps=eps, integrator=integ) as sim:
+            sim.upload(b)
+            sim.monitor_start(every=4, capacity=5)
+            sim.step(30)                                  # samples after steps 4, 8, 12, 16, 20 (capacity 5)
+            log = sim.monitor_read()
+            ke, pe, mom = sim.energy()
+            out = sim.download()
+        assert log.shape == (5, 8) and np.array_equal(log[:, 0], [4, 8, 12, 16, 20])
+        assert np.allclose(log[:, 1], log[:, 0] * dt)
+        step = oracle.run_kdk if integ == gs.INTEGRATOR_LEAPFROG else oracle.run_sync
+        ref4 = step(b.astype(np.float64), dt, 4, G=1.0, eps=eps)
+        oke, ope, omom = oracle.energy(ref4, G=1.0, eps=eps)
+        assert abs(log[0, 2] / oke - 1) <= 1e-4 and abs(log[0, 3] / ope - 1) <= 1e-5
+        assert np.abs(log[0, 4:7] - omom).max() <= 1e-6
+        E = log[:, 2] + log[:, 3]
+        assert np.abs(E / E[0] - 1).max() <= 1e-3
+        ref30 = step(b.astype(np.float64), dt, 30, G=1.0, eps=eps)   # sampling must not disturb the trajectory
+        assert np.abs(out[:, :3] - ref30[:, :3]).max() <= 2e-5 and np.abs(out[:, 3:6] - ref30[:, 3:6]).max() <= 2e-4
+
+
 def test_trajectory_recording(gs):
     b = gs.ic_reference_uniform(3001, seed=2)
     with gs.GravSim(3001) as sim:
@@ -580,7 +635,8 @@ def test_two_gpus_when_present(gs, oracle):
     b = gs.ic_reference_uniform(n, seed=31)
     ref = oracle.run_sync(b.astype(np.float64), 3600.0, 6)
     # peer-memory exchange (default), with the two-pass overlap schedule, and the NCCL all-gather fallback
-    for flags in (0, DET, gs.FLAG_OVERLAP, gs.FLAG_NCCL_EXCHANGE, gs.FLAG_NCCL_EXCHANGE | gs.FLAG_OVERLAP, gs.FLAG_COMPENSATED):
+    for flags in (0, DET, gs.FLAG_OVERLAP, gs.FLAG_NCCL_EXCHANGE, gs.FLAG_NCCL_EXCHANGE | gs.FLAG_OVERLAP, gs.FLAG_COMPENSATED,
+                  gs.FLAG_FP64_FORCES, gs.FLAG_FP64_FORCES | gs.FLAG_COMPENSATED):
         uid = gs.nccl_unique_id()
         res, errs = [None, None], []
 
@@ -589,8 +645,12 @@ def test_two_gpus_when_present(gs, oracle):
                 with gs.GravSim(n, device=rank, rank=rank, world_size=2, nccl_id=uid, flags=flags) as sim:
                     sim.upload(b)
                     a = sim.accel()
+                    sim.monitor_start(every=3, capacity=4)                    # on-device samples after steps 3 and 6
                     sim.step(6)
+                    log = sim.monitor_read()
                     e = sim.energy()
+                    assert log.shape == (2, 8) and log[1, 2] == e[0] and log[1, 3] == e[1]
+                    sim.monitor_start(0, 0)
                     assert sim.info.peer_exchange == (0 if flags & gs.FLAG_NCCL_EXCHANGE else 1)
                     out = sim.download()
                     frames = sim.step_trajectory(2, every=1)                 # collective, like step()
