@@ -236,10 +236,9 @@ int force_pass(gs_ctx* c, int final_mode, float kick, float drift, float4* acc_o
                 PeerFlags f;
                 for (int q = 0; q < W; ++q) f.slot[q] = c->peer_flags[q] + 16 + c->cfg.rank;
                 c->fstep++;
-                GS_CUDA(c, launch_signal_peers(f, W, c->cfg.rank, c->fstep, c->stream));
-                GS_CUDA(c, launch_wait_flags(c->flags + 16, W, c->cfg.rank, c->fstep, c->comm_timeout_ns, c->d_comm_err,
-                                             c->stream));
-                c->launches += 2;
+                GS_CUDA(c, launch_signal_wait(f, c->flags + 16, W, c->cfg.rank, c->fstep, c->comm_timeout_ns, c->d_comm_err,
+                                              c->stream));
+                c->launches++;
             }
             GS_CUDA(c, launch_sym_finish(p, sp, c->d_sym_rows, c->i_tile, &extras, c->stream)); c->launches++;
             return GS_OK;
@@ -269,8 +268,15 @@ int exchange_positions(gs_ctx* c, int nxt) {
         PeerFlags f;
         for (int q = 0; q < c->cfg.world_size; ++q) f.slot[q] = c->peer_flags[q] + c->cfg.rank;
         c->xstep++;
-        GS_CUDA(c, launch_signal_peers(f, c->cfg.world_size, c->cfg.rank, c->xstep, c->stream)); c->launches++;
-        c->wait_pending = true;
+        if (c->cfg.flags & GS_FLAG_OVERLAP) {      // own-slice work of the next pass may run before the wait
+            GS_CUDA(c, launch_signal_peers(f, c->cfg.world_size, c->cfg.rank, c->xstep, c->stream));
+            c->wait_pending = true;
+        } else {                                   // one launch for both halves of the round
+            GS_CUDA(c, launch_signal_wait(f, c->flags, c->cfg.world_size, c->cfg.rank, c->xstep, c->comm_timeout_ns,
+                                          c->d_comm_err, c->stream));
+            c->wait_pending = false;
+        }
+        c->launches++;
         return GS_OK;
     }
     NcclApi& nc = nccl_api();
@@ -307,7 +313,12 @@ int default_variant(int n, int world, int cut_mode, uint32_t flags) {
     if (units6 < 8 * 148) {
         // tiny problems: even 512-body i-tiles leave SMs idle -> 256-body i-tiles (R=2 x 128 threads)
         const int64_t units10 = ((int64_t)pad6 / world / 512) * (pad6 / kJTile);
-        return units10 < 4 * 148 ? 16 : 10;
+        if (units10 < 4 * 148) return 16;
+        // in between (N ~ 14K..30K per GPU-row band): the pair-symmetric pass on 1024-body i-tiles, 2 CTAs per SM
+        // (profiles/r2_small_n_probe.txt: N = 16,384 58.6 % vs 54-56 % for the row-gather variants)
+        const int64_t units1 = ((int64_t)pad1 / world / 1024) * (pad1 / kJTile);
+        if (!(flags & GS_FLAG_DETERMINISTIC) && world <= kMaxPeers + 1 && units1 >= 400) return 1;
+        return 10;
     }
     if (!(flags & GS_FLAG_DETERMINISTIC) && world <= kMaxPeers + 1) {
         // pair-symmetric pass (256 threads; measured at N = 1M, equal masses: R = 8 4.12e12, R = 6 3.88e12,

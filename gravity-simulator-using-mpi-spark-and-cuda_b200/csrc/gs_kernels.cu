@@ -351,6 +351,31 @@ __global__ void wait_flags_kernel(const uint32_t* my_flags, int world, int my_ra
     }
 }
 
+// Both halves of a flag round in one launch: lane q raises my counter on peer q, then waits for peer q's counter here.
+__global__ void signal_wait_kernel(PeerFlags f, const uint32_t* my_flags, int world, int my_rank, uint32_t value,
+                                   unsigned long long timeout_ns, uint32_t* err) {
+    const int q = threadIdx.x;
+    if (q >= world || q == my_rank) return;
+    __threadfence_system();
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(f.slot[q]), "r"(value) : "memory");
+    unsigned long long t0;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    for (;;) {
+        uint32_t v;
+        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(my_flags + q) : "memory");
+        if ((int32_t)(v - value) >= 0) break;
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        if (t - t0 > timeout_ns) { *err = 1u; break; }
+        __nanosleep(100);
+    }
+}
+cudaError_t launch_signal_wait(const PeerFlags& f, const uint32_t* my_flags, int world, int my_rank, uint32_t value,
+                               unsigned long long timeout_ns, uint32_t* err, cudaStream_t s) {
+    signal_wait_kernel<<<1, 32, 0, s>>>(f, my_flags, world, my_rank, value, timeout_ns, err);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_signal_peers(const PeerFlags& f, int world, int my_rank, uint32_t value, cudaStream_t s) {
     signal_peers_kernel<<<1, 32, 0, s>>>(f, world, my_rank, value);
     return cudaGetLastError();

@@ -84,6 +84,10 @@ cudaError_t launch_signal_peers(const PeerFlags& f, int world, int my_rank, uint
 cudaError_t launch_wait_flags(const uint32_t* my_flags, int world, int my_rank, uint32_t value,
                               unsigned long long timeout_ns, uint32_t* err, cudaStream_t s);
 
+// signal + wait of one flag round in a single launch
+cudaError_t launch_signal_wait(const PeerFlags& f, const uint32_t* my_flags, int world, int my_rank, uint32_t value,
+                               unsigned long long timeout_ns, uint32_t* err, cudaStream_t s);
+
 // ---- pair-symmetric force pass (gs_symmetric.cu; the default) --------------------------------------------------
 struct SymCta { int row0, k0, count, pad; };   // a persistent CTA's first unit (row, index in the row) and unit count
 struct SymParams {
