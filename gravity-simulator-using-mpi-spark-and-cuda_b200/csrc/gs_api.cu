@@ -463,8 +463,7 @@ int setup_symmetric(gs_ctx* c) {
     fill_sym_geometry(c, &geo);
     std::vector<SymCta> hc;
     std::vector<int2> hr;
-    int cost_plain = 100, cost_sym = 133;                 // issue cycles per unit, relative (34 vs 26 per j-pair and i-body)
-    if (const char* ev = getenv("GRAVSIM_SYM_COST")) cost_sym = atoi(ev);
+    const int cost_plain = 100, cost_sym = 133;           // issue cycles per unit, relative (34 vs 26 per j-pair and i-body)
     build_sym_plan(geo, c->sym_grid, cost_plain, cost_sym, hc, hr);
     const size_t slice_bytes = (size_t)c->slice * sizeof(float4);
     GS_CUDA(c, cudaMalloc((void**)&c->d_sym_ctas, hc.size() * sizeof(SymCta)));
@@ -684,7 +683,6 @@ int gs_create(gs_ctx** out, const gs_config* cfg) {
     if (!c) return GS_ENOMEM;
     c->cfg = *cfg;
     c->cfg.nccl_id = nullptr;
-    if (const char* ef = getenv("GRAVSIM_FLAGS")) c->cfg.flags |= (uint32_t)atoi(ef);   // experiments
     int rc = GS_OK;
     auto fail = [&](int code) { gs_destroy(c); return code; };
 
@@ -702,10 +700,7 @@ int gs_create(gs_ctx** out, const gs_config* cfg) {
     const char* ecm = getenv("GRAVSIM_CUTMODE");                        // "select" | "tracked": tests, A/B runs
     if (c->cut_mode != kSoftened && ecm && !strcmp(ecm, "select")) c->cut_mode = kCutoff;
     c->variant = cfg->variant;
-    if (c->variant == 0) {
-        const char* ev = getenv("GRAVSIM_VARIANT");
-        c->variant = ev ? atoi(ev) : default_variant(cfg->n, cfg->world_size, c->cut_mode, c->cfg.flags);
-    }
+    if (c->variant == 0) c->variant = default_variant(cfg->n, cfg->world_size, c->cut_mode, c->cfg.flags);
     VariantInfo vi;
     if (!variant_info(c->variant, &vi)) return fail(GS_EINVAL);
     c->R = vi.R;

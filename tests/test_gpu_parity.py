@@ -141,6 +141,21 @@ def test_fp32_range_sun_and_heavy_body(gs, oracle):
     assert np.isfinite(a).all() and rel_err(a, oracle.accel(b.astype(np.float64))).max() <= ACC_TOL
 
 
+def test_far_body_range(gs, oracle):
+    # SI units far from everything: the default pass forms rinv^3 in fp32 (denormal beyond 4.4e12 m, still 1e-6
+    # accurate at 1e13 m -- the reference's distribution spans 1e12 m); the row-gather kernel multiplies
+    # (mu * rinv) * rinv^2 and the fp64 mode has no limit at all
+    n = 3000
+    b = gs.ic_reference_uniform(n, seed=77)
+    for far, kws in ((1.0e13, (dict(variant=3), dict(flags=DET), dict(flags=gs.FLAG_FP64_FORCES))),
+                     (1.0e15, (dict(flags=DET), dict(flags=gs.FLAG_FP64_FORCES)))):
+        b[n - 1, :3] = (far, 0.0, 0.0)
+        ref = oracle.accel(b.astype(np.float64))
+        for kw in kws:
+            a = gpu_accel(gs, b, **kw)
+            assert np.isfinite(a).all() and rel_err(a, ref).max() <= ACC_TOL, (far, kw, rel_err(a, ref).max())
+
+
 @pytest.mark.parametrize("variant", list(range(1, 18)))
 def test_every_kernel_variant(gs, oracle, variant):
     b = gs.ic_reference_uniform(3000, seed=variant)

@@ -9,7 +9,7 @@ from __graft_entry__ import load_package  # noqa: E402
 
 gs = load_package()
 PEAK = 148 * 128 * 2 * 1.965e9
-KNOBS = ("GRAVSIM_SYM_NPAIR", "GRAVSIM_SYM_SHFL", "GRAVSIM_SYM_PROBE", "GRAVSIM_CUTMODE", "GRAVSIM_GRID", "GRAVSIM_SYM_COST")
+KNOBS = ("GRAVSIM_SYM_NPAIR", "GRAVSIM_SYM_SHFL", "GRAVSIM_CUTMODE", "GRAVSIM_GRID")
 
 
 def probe(n, variant, eps, flags, env, steps=None):
