@@ -85,6 +85,7 @@ struct gs_ctx {
     int sym_grid = 0, sym_regs = 0, sym_cut_mode = 0;
     SymCta* d_sym_ctas = nullptr;
     int2* d_sym_rows = nullptr;
+    float4* pos_scaled = nullptr;               // tracked cutoff (eps == 0): positions x 2^-10, rewritten every pass
     long long* d_accj = nullptr;                // j-side sums of MY bodies, wide fixed point (peers add into it over NVLink)
     long long* peer_accj[kMaxPeers + 1] = {};   // every rank's accj as seen from this GPU
     float4* sym_partial = nullptr;
@@ -231,6 +232,14 @@ int force_pass(gs_ctx* c, int final_mode, float kick, float drift, float4* acc_o
             sp.pos = c->pos[c->cur]; sp.acc_whole = c->acc_stage; sp.partial = c->sym_partial;
             for (int q = 0; q < W; ++q) sp.accj[q] = c->peer_accj[q];
             sp.ctas = c->d_sym_ctas; sp.eps2 = c->eps2; sp.cut2 = c->cut2; sp.mu_uniform = c->mu_uniform;
+            if (c->sym_cut_mode == kCutoffTracked) {
+                // the tracked cutoff finds close pairs by overflow: the kernel reads a copy scaled by 2^-10
+                // (all n_pad bodies, 32 B each: ~10 us at N = 1M); the kernel rescales its sums by kSymOutScale
+                GS_CUDA(c, launch_scale_positions(c->pos[c->cur], c->pos_scaled, c->n_pad, kSymPosScale, c->stream));
+                c->launches++;
+                sp.pos = c->pos_scaled;
+                sp.cut2 = c->cut2 * kSymPosScale * kSymPosScale;
+            }
             GS_CUDA(c, launch_sym_force(c->R, c->threads, c->sym_cut_mode, sp, c->sym_grid, c->stream)); c->launches++;
             if (W > 1) {    // my j-side sums are complete once every peer's force kernel has finished
                 PeerFlags f;
@@ -469,6 +478,7 @@ int setup_symmetric(gs_ctx* c) {
     GS_CUDA(c, cudaMalloc((void**)&c->d_sym_ctas, hc.size() * sizeof(SymCta)));
     GS_CUDA(c, cudaMalloc((void**)&c->d_sym_rows, hr.size() * sizeof(int2)));
     GS_CUDA(c, cudaMalloc((void**)&c->sym_partial, (size_t)c->sym_grid * 2 * c->i_tile * sizeof(float4)));
+    if (c->sym_cut_mode == kCutoffTracked) GS_CUDA(c, cudaMalloc((void**)&c->pos_scaled, (size_t)c->n_pad * sizeof(float4)));
     if (!c->acc_stage) GS_CUDA(c, cudaMalloc((void**)&c->acc_stage, slice_bytes));
     GS_CUDA(c, cudaMemcpy(c->d_sym_ctas, hc.data(), hc.size() * sizeof(SymCta), cudaMemcpyHostToDevice));
     GS_CUDA(c, cudaMemcpy(c->d_sym_rows, hr.data(), hr.size() * sizeof(int2), cudaMemcpyHostToDevice));
@@ -646,7 +656,7 @@ void gs_destroy(gs_ctx* c) {
     cudaFree(c->flags); cudaFree(c->d_comm_err);
     if (c->comm) nccl_api().CommDestroy(c->comm);
     cudaFree(c->pos[0]); cudaFree(c->pos[1]); cudaFree(c->vel); cudaFree(c->vel_full);
-    cudaFree(c->d_sym_ctas); cudaFree(c->d_sym_rows); cudaFree(c->d_accj); cudaFree(c->sym_partial);
+    cudaFree(c->d_sym_ctas); cudaFree(c->d_sym_rows); cudaFree(c->d_accj); cudaFree(c->sym_partial); cudaFree(c->pos_scaled);
     cudaFree(c->pos_lo); cudaFree(c->vel_lo); cudaFree(c->lo_full[0]); cudaFree(c->lo_full[1]);
     cudaFree(c->acc_local); cudaFree(c->acc_stage); cudaFree(c->acc_lo); cudaFree(c->acc_out); cudaFree(c->partial); cudaFree(c->mass);
     cudaFree(c->d_aos); cudaFree(c->d_energy); cudaFree(c->d_mu_mm); cudaFree(c->d_log);

@@ -473,6 +473,18 @@ __global__ void packed_to_aos_kernel(const float4* __restrict__ pos, const float
     }
 }
 
+__global__ void scale_positions_kernel(const float4* __restrict__ src, float4* __restrict__ dst, int npairs, float scale) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= npairs) return;
+    const float4 A = src[2 * p], B = src[2 * p + 1];
+    dst[2 * p] = make_float4(A.x * scale, A.y * scale, A.z * scale, A.w * scale);
+    dst[2 * p + 1] = make_float4(B.x * scale, B.y * scale, B.z, B.w);            // {z0, z1, mu0, mu1}
+}
+cudaError_t launch_scale_positions(const float4* src, float4* dst, int n_pad, float scale, cudaStream_t s) {
+    scale_positions_kernel<<<(n_pad / 2 + 255) / 256, 256, 0, s>>>(src, dst, n_pad / 2, scale);
+    return cudaGetLastError();
+}
+
 // {min, max} -> {min, ~max} behind them, so that ONE min-reduction over ranks gives both
 __global__ void pack_minmax_kernel(uint32_t* mm) { mm[2] = mm[0]; mm[3] = ~mm[1]; }
 cudaError_t launch_pack_minmax(uint32_t* mm4, cudaStream_t s) {

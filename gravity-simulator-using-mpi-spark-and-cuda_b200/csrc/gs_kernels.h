@@ -90,8 +90,10 @@ cudaError_t launch_signal_wait(const PeerFlags& f, const uint32_t* my_flags, int
 
 // ---- pair-symmetric force pass (gs_symmetric.cu; the default) --------------------------------------------------
 struct SymCta { int row0, k0, count, pad; };   // a persistent CTA's first unit (row, index in the row) and unit count
+constexpr float kSymPosScale = 1.0f / 1024.0f;              // tracked cutoff: positions scaled by 2^-10 ...
+constexpr float kSymOutScale = 1.0f / 1048576.0f;           // ... make every sum 2^20 too large (mu t d -> mu (2^30 t)(2^-10 d))
 struct SymParams {
-    const float4* pos;       // packed pairs, n_pad bodies (every rank's)
+    const float4* pos;       // packed pairs, n_pad bodies (every rank's); kCutoffTracked: the copy scaled by kSymPosScale
     float4* acc_whole;       // i-side sums of rows handled by a single CTA (float4 per local body)
     float4* partial;         // [grid][2][i_tile]: i-side sums of rows split between CTAs
     long long* accj[kMaxPeers + 1];   // per rank: j-side sums of ITS bodies, 3 x kFxLimbs words of wide fixed point per
@@ -150,7 +152,9 @@ cudaError_t launch_aos_to_packed(const void* aos, int record_bytes, int rec_firs
                                  int body_count, double G, const UploadTargets& dst, float4* vel_local, double* mass,
                                  int i_begin, int n_local_pad, float4* pos_lo_local, float4* vel_lo_local,
                                  uint32_t* mu_minmax, cudaStream_t s);
-cudaError_t launch_pack_minmax(uint32_t* mm4, cudaStream_t s);      // mm4[2] = mm4[0], mm4[3] = ~mm4[1]
+cudaError_t launch_pack_minmax(uint32_t* mm4, cudaStream_t s);
+// dst = src with x, y, z multiplied by `scale` (a power of two: exact), mu unchanged; n_pad bodies.
+cudaError_t launch_scale_positions(const float4* src, float4* dst, int n_pad, float scale, cudaStream_t s);      // mm4[2] = mm4[0], mm4[3] = ~mm4[1]
 // Records of bodies [body_first, body_first + count) into aos[0..count): pos and mass are indexed globally, vel and
 // the (nullable) low-order words with (body - vel_first).
 cudaError_t launch_packed_to_aos(const float4* pos, const float4* vel, int vel_first, const double* mass,

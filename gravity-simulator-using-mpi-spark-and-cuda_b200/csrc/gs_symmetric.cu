@@ -38,10 +38,14 @@ constexpr size_t sym_smem_for(int threads) {
 // How the reference's "r < 1e-10 contributes nothing" (cuda.cu:39, mpi.c:64) is applied inside a symmetric unit
 // when eps == 0:
 //   kSymSelect: rinv = (r^2 >= 1e-20) ? rsqrt(r^2) : 0 on every interaction (2 FSETP + 2 FSEL per j-pair and i-body);
-//   kSymTrack : no select; one FMNMX3 per j-pair and i-body remembers the smallest r^2 the lane saw, and the warp
-//               redoes the unit with kSymSelect when anything came closer than the cutoff.  In a symmetric unit the
-//               i-tile and the j-tile are different tiles, so a body never meets itself there: a redo needs two
-//               distinct bodies within 1e-10 of each other, i.e. (in fp32) coincident bodies.
+//   kSymTrack : no select and no extra instruction.  The kernel reads positions scaled by 2^-10 (SymParams::pos is
+//               then a scaled copy, kSymOutScale = 2^-20 undoes it: powers of two, exact), so rinv is 2^10 times larger
+//               and rinv^3 OVERFLOWS to +inf for every pair with r < 1.46e-10 -- a superset of the pairs the rule
+//               removes (r < 1e-10).  inf (or NaN = inf * 0) then poisons the i-side sums of that lane; the warp
+//               checks its tile sums once per tile and redoes the unit with kSymSelect if any is not finite.
+//               In a symmetric unit the i-tile and the j-tile are different tiles, so a body never meets itself
+//               there: a redo needs two distinct bodies within 1.46e-10 of each other (in fp32: coincident bodies,
+//               or tiny separations next to the origin).
 enum SymCut : int { kSymSoft = 0, kSymSelect = 1, kSymTrack = 2 };
 
 // One j-tile, both directions.  NPAIR j-pairs per lane and iteration (pairs q, q+32, ... of a 32*NPAIR-pair chunk,
@@ -61,14 +65,11 @@ __device__ __forceinline__ bool sym_tile(const float4* __restrict__ T, float4* _
                                          const float2 (&nyi)[R], const float2 (&nzi)[R], const float2 (&nmui)[R],
                                          float2 eps2, float cut2, Acc<R>& out) {
     float2 ax[R], ay[R], az[R];
-    float rmin[NPAIR];
 #pragma unroll
     for (int b = 0; b < R; ++b) ax[b] = ay[b] = az[b] = make_float2(0.f, 0.f);
-#pragma unroll
-    for (int h = 0; h < NPAIR; ++h) rmin[h] = 3.0e38f;
     const int from = (lane + 1) & 31;       // the lane that worked on "my next pair" in this iteration
     // one j-pair (records A, B) against the R i-bodies, both directions
-    auto pair_step = [&](const float4& A, const float4& B, float2& jx, float2& jy, float2& jz, float& rm) {
+    auto pair_step = [&](const float4& A, const float4& B, float2& jx, float2& jy, float2& jz) {
         const float2 xj = make_float2(A.x, A.y), yj = make_float2(A.z, A.w);
         const float2 zj = make_float2(B.x, B.y), mj = make_float2(B.z, B.w);
 #pragma unroll
@@ -84,7 +85,6 @@ __device__ __forceinline__ bool sym_tile(const float4* __restrict__ T, float4* _
                 ri.x = (r2.x >= cut2) ? ri.x : 0.f;
                 ri.y = (r2.y >= cut2) ? ri.y : 0.f;
             }
-            if (CUT == kSymTrack) asm("min.f32 %0, %0, %1, %2;" : "+f"(rm) : "f"(r2.x), "f"(r2.y));   // FMNMX3
             const float2 ri2 = __fmul2_rn(ri, ri);
             const float2 t = __fmul2_rn(ri2, ri);                       // rinv^3, shared by both directions
             const float2 s = UNI ? t : __fmul2_rn(mj, t);               // on i:  +mu_j t d
@@ -110,7 +110,7 @@ __device__ __forceinline__ bool sym_tile(const float4* __restrict__ T, float4* _
 #pragma unroll
                 for (int h = 0; h < NPAIR; ++h) { A[h] = T[2 * (p0 + 32 * h)]; B[h] = T[2 * (p0 + 32 * h) + 1]; }
 #pragma unroll
-                for (int h = 0; h < NPAIR; ++h) pair_step(A[h], B[h], jx[h], jy[h], jz[h], rmin[h]);
+                for (int h = 0; h < NPAIR; ++h) pair_step(A[h], B[h], jx[h], jy[h], jz[h]);
                 // (measured: issuing each group's shuffles right after the group, with the next iteration's first
                 // loads prefetched, is 2.5 % slower -- ptxas sinks them to the end anyway and the loop gets longer)
 #pragma unroll
@@ -141,7 +141,7 @@ __device__ __forceinline__ bool sym_tile(const float4* __restrict__ T, float4* _
                     jx[h] = make_float2(JA.x, JA.y); jy[h] = make_float2(JA.z, JA.w); jz[h] = accB[p0 + 32 * h];
                 }
 #pragma unroll
-                for (int h = 0; h < NPAIR; ++h) pair_step(A[h], B[h], jx[h], jy[h], jz[h], rmin[h]);
+                for (int h = 0; h < NPAIR; ++h) pair_step(A[h], B[h], jx[h], jy[h], jz[h]);
 #pragma unroll
                 for (int h = 0; h < NPAIR; ++h) {
                     accA[p0 + 32 * h] = make_float4(jx[h].x, jx[h].y, jy[h].x, jy[h].y);
@@ -152,10 +152,11 @@ __device__ __forceinline__ bool sym_tile(const float4* __restrict__ T, float4* _
         }
     }
     if (CUT == kSymTrack) {
-        float m = rmin[0];
+        float2 c = make_float2(0.f, 0.f);         // inf and NaN survive a sum
 #pragma unroll
-        for (int h = 1; h < NPAIR; ++h) m = fminf(m, rmin[h]);
-        if (__any_sync(0xffffffffu, !(m >= cut2))) return true;
+        for (int b = 0; b < R; ++b) c = __fadd2_rn(__fadd2_rn(c, ax[b]), __fadd2_rn(ay[b], az[b]));
+        const float cs = c.x + c.y;
+        if (__any_sync(0xffffffffu, !(fabsf(cs) <= 3.0e38f))) return true;
     }
 #pragma unroll
     for (int b = 0; b < R; ++b) {
@@ -268,7 +269,7 @@ __global__ void __launch_bounds__(THREADS, 1) sym_force_kernel(const SymParams p
                 // accj layout: per j-tile, word (component * kFxLimbs + limb) * kJTile + body: consecutive lanes =
                 // consecutive bodies = consecutive words, so each of the integer atomics below is one coalesced request
                 long long* const jbase = p.accj[owner] + (size_t)kFxWordsPerBody * (size_t)(jtile - owner * p.slice_tiles) * kJTile;
-                const float w = UNI ? -p.mu_uniform : 1.f;
+                const float w = (UNI ? -p.mu_uniform : 1.f) * (CUT == kSymTrack ? kSymOutScale : 1.f);
                 for (int body = tid; body < kJTile; body += THREADS) {
                     const int e = body >> 1;
                     const bool odd = (body & 1) != 0;
@@ -307,7 +308,7 @@ __global__ void __launch_bounds__(THREADS, 1) sym_force_kernel(const SymParams p
 #pragma unroll
         for (int q = 0; q < NP; ++q) {
             const int in_tile = 2 * (q * THREADS + tid);
-            const float w = UNI ? p.mu_uniform : 1.f;
+            const float w = (UNI ? p.mu_uniform : 1.f) * (CUT == kSymTrack ? kSymOutScale : 1.f);
             const float4 a0 = make_float4(w * acc.x[2 * q], w * acc.y[2 * q], w * acc.z[2 * q], 0.f);
             const float4 a1 = make_float4(w * acc.x[2 * q + 1], w * acc.y[2 * q + 1], w * acc.z[2 * q + 1], 0.f);
             float4* dst = whole ? p.acc_whole + (size_t)row * ITILE + in_tile
