@@ -543,44 +543,66 @@ __device__ __forceinline__ double block_sum(double v, double* red) {
     return t;   // valid in thread 0
 }
 
-// One i-body per thread against every j-tile; fp32 pair terms, a 64-term fp32 partial, fp64 above.
-__global__ void __launch_bounds__(kEThreads) potential_kernel(const float4* __restrict__ pos, int n_pad, int i_begin,
-                                                              float eps2, float cut2, double* out_partials) {
-    __shared__ float4 tile[kJTile];
-    __shared__ double red[kEThreads / 32];
-    const int i = i_begin + blockIdx.x * kEThreads + threadIdx.x;
-    const float4 IA = pos[2 * (i >> 1)], IB = pos[2 * (i >> 1) + 1];
-    const bool odd = (i & 1) != 0;
-    const float xi = odd ? IA.y : IA.x, yi = odd ? IA.w : IA.z, zi = odd ? IB.y : IB.x, mui = odd ? IB.w : IB.z;
-    double pot = 0.0;
+// One i-PAIR per thread (256 bodies per CTA) against every j-tile, packed f32x2 like the force kernels: per j-pair
+// and i-body 3 FADD2 + 3 FFMA2 + 2 MUFU.RSQ + 1 FFMA2; fp32 pair terms, one fp32 partial per j-tile, fp64 above.
+// SOFT (eps > 0): no select at all -- the body's own term mu_i / eps is subtracted afterwards.
+// !SOFT (eps == 0): pairs with r^2 < cut2 (the body itself, coincident bodies) contribute nothing (cuda.cu:39, mpi.c:64).
+constexpr int kPotThreads = 128;
+template <bool SOFT>
+__global__ void __launch_bounds__(kPotThreads) potential_kernel(const float4* __restrict__ pos, int n_pad, int i_begin,
+                                                                float eps2, float cut2, double* out_partials) {
+    __shared__ __align__(16) float4 tile[kJTile];
+    __shared__ double red[kPotThreads / 32];
+    const int pair = ((i_begin + blockIdx.x * 2 * kPotThreads) >> 1) + threadIdx.x;
+    const float4 IA = pos[2 * pair], IB = pos[2 * pair + 1];
+    const float2 nx[2] = {make_float2(-IA.x, -IA.x), make_float2(-IA.y, -IA.y)};
+    const float2 ny[2] = {make_float2(-IA.z, -IA.z), make_float2(-IA.w, -IA.w)};
+    const float2 nz[2] = {make_float2(-IB.x, -IB.x), make_float2(-IB.y, -IB.y)};
+    const float2 e2 = make_float2(eps2, eps2);
+    double pot[2] = {0.0, 0.0};
     for (int j0 = 0; j0 < n_pad; j0 += kJTile) {
         __syncthreads();
-        for (int t = threadIdx.x; t < kJTile; t += kEThreads) tile[t] = pos[j0 + t];
+        for (int t = threadIdx.x; t < kJTile; t += kPotThreads) tile[t] = pos[j0 + t];
         __syncthreads();
-        for (int c = 0; c < kJTile / 2; c += 32) {
-            float part = 0.f;
+        float2 part[2] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
 #pragma unroll 4
-            for (int jp = c; jp < c + 32; ++jp) {
-                const float4 A = tile[2 * jp], B = tile[2 * jp + 1];
-                const int j = j0 + 2 * jp;
-                {
-                    const float dx = A.x - xi, dy = A.z - yi, dz = B.x - zi;
-                    const float d2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
-                    const float ri = rsqrt_approx(d2 + eps2);
-                    part += (j != i && d2 >= cut2) ? B.z * ri : 0.f;
+        for (int jp = 0; jp < kJTile / 2; ++jp) {
+            const float4 A = tile[2 * jp], B = tile[2 * jp + 1];
+            const float2 xj = make_float2(A.x, A.y), yj = make_float2(A.z, A.w);
+            const float2 zj = make_float2(B.x, B.y), mj = make_float2(B.z, B.w);
+#pragma unroll
+            for (int b = 0; b < 2; ++b) {
+                const float2 dx = __fadd2_rn(xj, nx[b]), dy = __fadd2_rn(yj, ny[b]), dz = __fadd2_rn(zj, nz[b]);
+                float2 r2 = __ffma2_rn(dx, dx, e2);
+                r2 = __ffma2_rn(dy, dy, r2);
+                r2 = __ffma2_rn(dz, dz, r2);
+                float2 ri = make_float2(rsqrt_approx(r2.x), rsqrt_approx(r2.y));
+                if (!SOFT) {
+                    ri.x = (r2.x >= cut2) ? ri.x : 0.f;
+                    ri.y = (r2.y >= cut2) ? ri.y : 0.f;
                 }
-                {
-                    const float dx = A.y - xi, dy = A.w - yi, dz = B.y - zi;
-                    const float d2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
-                    const float ri = rsqrt_approx(d2 + eps2);
-                    part += (j + 1 != i && d2 >= cut2) ? B.w * ri : 0.f;
-                }
+                part[b] = __ffma2_rn(mj, ri, part[b]);
             }
-            pot += (double)part;
         }
+        pot[0] += (double)part[0].x + (double)part[0].y;
+        pot[1] += (double)part[1].x + (double)part[1].y;
     }
-    const double total = block_sum(pot * (double)mui, red);
-    if (threadIdx.x == 0) out_partials[blockIdx.x] = total;
+    const double mu0 = IB.z, mu1 = IB.w;
+    if (SOFT) {                  // the term of the body with itself: d = 0, so r2 was exactly eps2
+        const double self = (double)rsqrt_approx(eps2);
+        pot[0] -= mu0 * self;
+        pot[1] -= mu1 * self;
+    }
+    double v = mu0 * pot[0] + mu1 * pot[1];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int i = 0; i < kPotThreads / 32; ++i) t += red[i];
+        out_partials[blockIdx.x] = t;
+    }
 }
 
 __global__ void __launch_bounds__(kEThreads) kinetic_kernel(const float4* __restrict__ vel_local,
@@ -634,7 +656,9 @@ int energy_grid(int n_local_pad) { return n_local_pad / kEThreads; }
 
 cudaError_t launch_potential(const float4* pos, int n_pad, int i_begin, int n_local_pad, float eps2, float cut2,
                              double* out_partials, cudaStream_t s) {
-    potential_kernel<<<energy_grid(n_local_pad), kEThreads, 0, s>>>(pos, n_pad, i_begin, eps2, cut2, out_partials);
+    static_assert(2 * kPotThreads == kEThreads, "one partial per 256 bodies (energy_grid, gs_noalloc.cu)");
+    if (eps2 > 0.f) potential_kernel<true><<<energy_grid(n_local_pad), kPotThreads, 0, s>>>(pos, n_pad, i_begin, eps2, cut2, out_partials);
+    else potential_kernel<false><<<energy_grid(n_local_pad), kPotThreads, 0, s>>>(pos, n_pad, i_begin, eps2, cut2, out_partials);
     return cudaGetLastError();
 }
 cudaError_t launch_kinetic(const float4* vel_local, const double* mass, int i_begin, int n_local_pad, double* out4,
