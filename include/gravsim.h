@@ -70,10 +70,11 @@ typedef struct gs_config {
 #define GS_FLAG_NO_UNIFORM_MASS 4u /* keep the general kernel even when all masses are equal        */
 #define GS_FLAG_OVERLAP    8u   /* multi-GPU: own j-slice first, remote slices after the exchange  */
 #define GS_FLAG_NCCL_EXCHANGE 16u /* multi-GPU: per-step ncclAllGather instead of peer-memory stores */
-#define GS_FLAG_DETERMINISTIC 128u /* bit-reproducible sums: use the row-gather kernel instead of the default
-                                   pair-symmetric pass (every unordered pair once, applied to both bodies as
-                                   cuda.cu:43-49 does -- ~1.3x faster, but its floating-point atomics make the
-                                   last bits depend on timing)                                             */
+#define GS_FLAG_DETERMINISTIC 128u /* use the row-gather kernel (every ORDERED pair like mpi.c:196-204, no atomics of
+                                   any kind, per-body sums in a fixed order) instead of the default pair-symmetric
+                                   pass.  0.7x the speed.  The default pass is bit-reproducible as well (its
+                                   cross-CTA / cross-GPU sums are exact integer atomics), but only for a fixed
+                                   configuration (N, GPU count); its rounding differs from the row-gather kernel's */
 #define GS_FLAG_COMPENSATED 32u /* positions and velocities as hi+lo fp32 pairs: the integration no longer
                                    rounds to the state's fp32 ulp each step (forces stay fp32); f64 records
                                    keep their low-order bits through upload/download                    */
@@ -140,8 +141,8 @@ int gs_download_slice_f64(gs_ctx *ctx, void *my_particles56, int first, int coun
 
 /* Replaces the step loops cuda.cu:155-163 (kernel, sync, D2H, host update) and mpi.c:191-237
  * (force rows, in-place update, MPI_Allgatherv, MPI_Barrier).  By default every unordered pair is
- * evaluated once and applied to both bodies (cuda.cu:43-49, without its race; GS_FLAG_DETERMINISTIC
- * evaluates ordered pairs like mpi.c:196-204 and is bit-reproducible).  All bodies advance from the
+ * evaluated once and applied to both bodies (cuda.cu:43-49, without its race, and bit-reproducible;
+ * GS_FLAG_DETERMINISTIC evaluates ordered pairs like mpi.c:196-204).  All bodies advance from the
  * same snapshot (synchronous step; see DESIGN.md on mpi.c's in-place order).  Asynchronous:
  * returns after enqueueing; no per-step host synchronisation or D2H. */
 int gs_step(gs_ctx *ctx, int nsteps);

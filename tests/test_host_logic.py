@@ -182,3 +182,46 @@ def test_cli_driver_built_and_fails_loudly_without_gpu(gs):
     if not torch.cuda.is_available():
         r = subprocess.run([exe, "64", "1", "3600", "--quiet"], capture_output=True, text=True)
         assert r.returncode == 1 and "no CUDA device" in r.stderr
+
+
+def test_bench_reference_arm_line_and_its_bodies(gs):
+    """bench.py --impl reference: honest config (what it ran), zero GPU bytes, and bodies generated without the
+    product library in the reference's own distribution (same Sun/Earth/Mars records as the library's generator)."""
+    import importlib.util
+    import json
+    import sys
+    spec = importlib.util.spec_from_file_location("bench_mod", os.path.join(REPO, "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    b = bench.reference_uniform_numpy(1000, seed=3)
+    assert np.array_equal(b[:3].astype(np.float32), gs.ic_reference_uniform(3, seed=1))
+    assert np.abs(b[3:, :3]).max() <= 3e11 and np.abs(b[3:, 3:6]).max() <= 3e4
+    assert b[3:, 6].min() >= 1e23 and b[3:, 6].max() <= 1e25 and np.array_equal(b, b.astype(np.float32).astype(np.float64))
+    if not os.path.exists(os.path.join(REPO, "oracle", "_ref", "mpi_ref")):
+        pytest.skip("oracle/_ref not built (needs /root/reference)")
+    r = subprocess.run([sys.executable, os.path.join(REPO, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0"],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr
+    line = json.loads(r.stdout.strip().splitlines()[-1])
+    assert line["impl"] == "reference" and line["config"]["workload"] == "reference_uniform_n32768_eps0_sample"
+    assert line["config"]["extrapolated"] is True and line["value"] > 0 and line["unit"] == "interactions/s"
+    assert line["e2e"]["h2d_bytes_per_step"] == 0 and line["cpu_baseline"]["kind"] == "reference"
+
+
+def test_merge_sweep_efficiencies(tmp_path):
+    import json
+    import sys
+    rows = lambda p, scale: [{"n_bodies": n, "n_gpus": p, "ms_per_step": 1e-9 * n * n / (p * scale), "value": 1e12 * p * scale,
+                              "pct_fp32_peak_per_gpu": 100.0 * scale} for n in (16384, 32768)]
+    files = []
+    for p, scale in ((1, 1.0), (4, 0.9)):
+        f = tmp_path / f"s{p}.json"
+        f.write_text(json.dumps({"metric": "m", "unit": "u", "config": {}, "rows": rows(p, scale)}) + "\n")
+        files.append(str(f))
+    out = tmp_path / "merged.json"
+    r = subprocess.run([sys.executable, os.path.join(REPO, "tools", "merge_sweep.py"), str(out)] + files, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    m = {(x["n_bodies"], x["n_gpus"]): x for x in json.load(open(out))["rows"]}
+    assert abs(m[(32768, 4)]["strong_efficiency"] - 0.9) < 1e-9
+    assert abs(m[(32768, 4)]["weak_efficiency_vs_half_n_quarter_p"] - 0.9) < 1e-9
+    assert m[(16384, 1)]["strong_efficiency"] == 1.0 and m[(16384, 4)]["weak_efficiency_vs_half_n_quarter_p"] is None
