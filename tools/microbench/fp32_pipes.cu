@@ -152,6 +152,54 @@ __global__ void __launch_bounds__(256) k_ffma2_mufu(float* out, float b, float c
     out[blockIdx.x * blockDim.x + threadIdx.x] = s;
 }
 
+// The pair-symmetric inner step itself, registers only (no shared memory, no shuffles, no loop-carried addressing):
+// per (i-body, j-pair) 3 FADD2 + 3 FFMA2 + 2 MUFU.RSQ + 2 FMUL2 + 6 FFMA2 with the kernel's dependency chains
+// (DESIGN.md 4.1b).  R i-bodies x NP j-pairs independent chains per iteration.  Lane-ops counted for the 14 packed
+// instructions only: 128/clk/SM = FMA pipe full.  This is the ceiling of the instruction stream, before any data movement.
+template <int R, int NP>
+__global__ void __launch_bounds__(256) k_symstep(float* out, float b, float c) {
+    float2 nx[R], ny[R], nz[R], ax[R], ay[R], az[R];
+    float2 xj[NP], yj[NP], zj[NP], jx[NP], jy[NP], jz[NP];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        nx[r] = make_float2(-(threadIdx.x * 1e-3f + r), -(threadIdx.x * 1e-3f + r));
+        ny[r] = make_float2(-(r * 0.37f + b), -(r * 0.37f + b));
+        nz[r] = make_float2(-(r * 0.11f + c), -(r * 0.11f + c));
+        ax[r] = ay[r] = az[r] = make_float2(0.f, 0.f);
+    }
+#pragma unroll
+    for (int h = 0; h < NP; ++h) {
+        xj[h] = make_float2(100.f + h + threadIdx.x, 101.f + h); yj[h] = make_float2(50.f + h, 51.f - h);
+        zj[h] = make_float2(25.f + h, 26.f + h); jx[h] = jy[h] = jz[h] = make_float2(0.f, 0.f);
+    }
+    const float2 eps2 = make_float2(c, c), drift = make_float2(b * 1e-3f, b * 1e-3f);
+    for (int it = 0; it < ITERS / 8; ++it) {
+#pragma unroll
+        for (int h = 0; h < NP; ++h) {
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                const float2 dx = __fadd2_rn(xj[h], nx[r]), dy = __fadd2_rn(yj[h], ny[r]), dz = __fadd2_rn(zj[h], nz[r]);
+                float2 r2 = __ffma2_rn(dx, dx, eps2);
+                r2 = __ffma2_rn(dy, dy, r2);
+                r2 = __ffma2_rn(dz, dz, r2);
+                float2 ri;
+                asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(ri.x) : "f"(r2.x));
+                asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(ri.y) : "f"(r2.y));
+                const float2 t = __fmul2_rn(__fmul2_rn(ri, ri), ri);
+                ax[r] = __ffma2_rn(t, dx, ax[r]); ay[r] = __ffma2_rn(t, dy, ay[r]); az[r] = __ffma2_rn(t, dz, az[r]);
+                jx[h] = __ffma2_rn(t, dx, jx[h]); jy[h] = __ffma2_rn(t, dy, jy[h]); jz[h] = __ffma2_rn(t, dz, jz[h]);
+            }
+            xj[h] = __fadd2_rn(xj[h], drift);      // "the next pair": keeps the loop body from being hoisted (1 extra FADD2 per R)
+        }
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int r = 0; r < R; ++r) s += ax[r].x + ax[r].y + ay[r].x + ay[r].y + az[r].x + az[r].y;
+#pragma unroll
+    for (int h = 0; h < NP; ++h) s += jx[h].x + jx[h].y + jy[h].x + jy[h].y + jz[h].x + jz[h].y;
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
 template <typename K>
 static void run(const char* name, K kern, int blocks_per_sm, double ops_per_thread_iter, int sms, float* d_out) {
     int grid = sms * blocks_per_sm;
@@ -180,6 +228,12 @@ int main() {
     int sms = p.multiProcessorCount;
     printf("device %s, %d SMs, clockRate %d kHz\n", p.name, sms, p.clockRate);
     float* d_out; CK(cudaMalloc(&d_out, (size_t)sms * 8 * 256 * sizeof(float)));
+    // the symmetric inner step: 8 warps per SM as in the shipped kernel (its registers allow one 256-thread block)
+    for (int bps : {1}) {
+        run("symstep R=8 NP=4 (packed lanes)", k_symstep<8, 4>, bps, 8 * 4 * 28 / 8.0, sms, d_out);
+        run("symstep R=8 NP=2 (packed lanes)", k_symstep<8, 2>, bps, 8 * 2 * 28 / 8.0, sms, d_out);
+        run("symstep R=4 NP=4 (packed lanes)", k_symstep<4, 4>, bps, 4 * 4 * 28 / 8.0, sms, d_out);
+    }
     for (int bps : {2, 4}) {
         run("ffma  (reg,const,const) ILP8", k_ffma<8>, bps, 8, sms, d_out);
         run("ffma3 (3 distinct regs) ILP8", k_ffma3<8>, bps, 8, sms, d_out);
