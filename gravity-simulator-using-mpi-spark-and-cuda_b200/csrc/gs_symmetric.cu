@@ -2,16 +2,17 @@
 // pair of bodies in different tiles is evaluated ONCE and applied to both bodies (Newton's third law), which the
 // reference's cuda.cu also does (cuda.cu:43-49) -- there with a data race, here without.
 //
-// Why it pays: the kernel is issue-bound.  A (i-body, j-pair) step costs 26 issue cycles for
-// two directed interactions in the row-gather kernel; sharing d, r^2, rsqrt and rinv^3 between the two
-// directions costs 34 for four.  The usual objection -- the j-side sums need a reduction across the 32 lanes
-// that all look at the same j -- is avoided by ROTATING the j-pairs over the lanes: in iteration `it` lane l
-// works on j-pair (it + l) mod 32 of the current 64-pair chunk (and on that pair + 32), so no two lanes of a
-// warp touch the same j at the same time and each lane simply read-modify-writes that pair's running sums in a
-// per-warp shared-memory accumulator array (conflict-free: consecutive lanes, consecutive entries).
-// After a j-tile the eight warps' arrays are added up and sent to global memory with atomic adds
-// (floating-point atomics: the last bits depend on timing; local memory, or NVLink peer memory when the j-bodies
-// belong to another GPU).
+// Why it pays: the kernel is bound by the FP32 FMA pipe.  A (i-body, j-pair) step costs 12 packed
+// instructions + 2 MUFU for two directed interactions in the row-gather kernel; sharing d, r^2, rsqrt and rinv^3
+// between the two directions costs 14 + 2 for four.  The usual objection -- the j-side sums need a reduction across
+// the 32 lanes that all look at the same j -- is avoided by ROTATING the j-pairs over the lanes: in iteration `it`
+// lane l works on j-pair (it + l) mod 32 of the current 128-pair chunk (and on that pair + 32, + 64, + 96), so no two
+// lanes of a warp touch the same j at the same time.  A pair's running sums follow it from lane to lane by warp
+// shuffles and are stored once per chunk into a per-warp shared-memory array.
+// After a j-tile the warps' arrays are added up and added into the owner's j-side sums in global memory -- local
+// memory, or NVLink peer memory when the j-bodies belong to another GPU -- as exact wide fixed point with 64-bit
+// integer atomics (gs_device.cuh, fx_add): the result does not depend on the order of arrival, so the pass is
+// bit-reproducible.
 //
 // Work: rows of (i-tile x j-tile) units; row I starts with its `diag` = i_tile/j_tile own j-tiles, done as
 // plain (one-directional, all ordered pairs) units, followed by symmetric units for every later j-tile of the
