@@ -451,7 +451,7 @@ void peer_exchange_goodbye(gs_ctx* c) {
     c->xstep++;
     launch_signal_peers(f, c->cfg.world_size, c->cfg.rank, c->xstep, c->stream);
     launch_wait_flags(c->flags, c->cfg.world_size, c->cfg.rank, c->xstep, 5000000000ull, c->d_comm_err, c->stream);
-    cudaStreamSynchronize(c->stream);
+    cudaStreamSynchronize(c->stream);      // a peer that is gone already costs the 5 s above, nothing else: we are leaving too
 }
 
 // Second half of the pair-symmetric set-up, once it is known whether peers can be reached with atomics.

@@ -12,7 +12,10 @@
  *     gs_strerror() names the code, gs_last_cuda_error() gives the cudaError_t behind GS_ECUDA.
  *   - the library owns all device memory, streams and NCCL communicators behind gs_ctx;
  *     host buffers stay caller-owned and are only touched during the call.
- *   - a gs_ctx is used from one host thread at a time; one ctx drives one GPU.
+ *   - a gs_ctx is used from one host thread at a time; one ctx drives one GPU.  With world_size > 1 every rank
+ *     needs its own host thread or process, as the ranks of mpirun have: uploads, downloads and gs_energy
+ *     synchronise while they wait for the peers, so one thread driving several ranks in turn would wait for itself
+ *     (and get GS_ENCCL after the peer timeout).
  *   - there is NO CPU fallback: without a usable CUDA device gs_create fails with GS_ENOGPU.
  *
  * Body records accepted/produced (the reference's own structs, byte for byte):
